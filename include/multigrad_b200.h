@@ -1,0 +1,176 @@
+/*
+ * multigrad_b200 -- C ABI of the sm_100a kernel library (libmgb200.so).
+ *
+ * Every entry point is `extern "C"`, takes raw device pointers plus a
+ * `cudaStream_t` (passed as void*), runs on the *current* CUDA device and
+ * returns 0 on success or a negative MGB_E* / positive cudaError_t code.
+ * `mgb_last_error()` returns a human readable message for the calling thread.
+ *
+ * The reference (AlanPearl/multigrad) contains no native code at all
+ * (SURVEY.md section 2.0); the comment above each declaration names the
+ * Python component of the reference whose work the kernel replaces.
+ */
+#ifndef MULTIGRAD_B200_H_
+#define MULTIGRAD_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGB_MAX_WORLD 16   /* ranks in one peer workspace (one NVSwitch box)  */
+#define MGB_MAX_BINS 32    /* soft bins per model in the fused kernels        */
+#define MGB_MAX_PARAMS 8   /* parameter-vector length of the scalar-link path */
+#define MGB_MAX_BATCH 4096 /* parameter vectors per batched evaluation        */
+
+/* error codes (negative; positive values are cudaError_t) */
+#define MGB_OK 0
+#define MGB_EINVAL (-1)
+#define MGB_ETOOBIG (-2)
+#define MGB_ETIMEOUT (-3)
+#define MGB_ESTATE (-4)
+
+const char* mgb_last_error(void);
+int mgb_version(void);
+
+/* ------------------------------------------------------------------------
+ * Peer workspace (N1).  Replaces the MPI communicator plumbing of the
+ * reference (multigrad/multigrad.py:15-27, 88-146): one cudaMalloc'ed block
+ * per rank, exported with CUDA IPC so that every rank of a (sub)communicator
+ * can load/store every other rank's block over NVLink from inside kernels.
+ * Layout: [ctrl 4 KiB][LL slots: 2 parities x world x ll_units x 8 B]
+ *         [bulk region: bulk_bytes][bulk region 2: bulk_bytes].
+ * ---------------------------------------------------------------------- */
+typedef struct MgbPeerTable {
+  int32_t world;            /* ranks in this workspace                       */
+  int32_t rank;             /* this rank                                     */
+  uint32_t ll_units;        /* 8-byte LL slots per (parity, source rank)     */
+  uint32_t spin_timeout_ms; /* watchdog for every in-kernel wait             */
+  uint64_t bulk_bytes;      /* size of each of the two bulk regions          */
+  void* base[MGB_MAX_WORLD];/* workspace base of every rank (peer-mapped)    */
+} MgbPeerTable;
+
+uint64_t mgb_ws_bytes(int world, uint32_t ll_units, uint64_t bulk_bytes);
+int mgb_ws_alloc(uint64_t bytes, void** out_ptr);
+int mgb_ws_free(void* ptr);
+int mgb_ws_export(void* ptr, uint8_t handle_out[64]);
+int mgb_ws_import(const uint8_t handle[64], void** out_ptr);
+int mgb_ws_unimport(void* ptr);
+/* reads ctrl word `idx` (0 epoch, 1 error, 2 bulk epoch) of a local block */
+int mgb_ws_read_ctrl(const void* local_base, int idx, uint32_t* out,
+                     void* stream);
+
+/* ------------------------------------------------------------------------
+ * K5: stand-alone all-reduce (sum) over the peer workspace.  Replaces
+ * reduce_sum's np.asarray + MPI Allreduce (multigrad/multigrad.py:149-183).
+ * dtype: 0 = float32, 1 = float64.  In place on `data` (n elements).
+ * Small messages use the one-shot ordered LL exchange (bit-identical result
+ * on every rank); larger ones the two-shot reduce-scatter + all-gather over
+ * peer loads/stores.  `algo`: 0 auto, 1 force LL, 2 force two-shot.
+ * ---------------------------------------------------------------------- */
+int mgb_allreduce_sum(const MgbPeerTable* pt, void* data, uint64_t n,
+                      int dtype, int algo, void* stream);
+/* push `n` floats from `root` to every rank (K6, BFGS parameter hand-off;
+ * replaces the pickled "compute"/params bcast of multigrad/bfgs.py:72-77).
+ * Non-root ranks wait on the GPU until the data arrives. */
+int mgb_bcast_f32(const MgbPeerTable* pt, float* data, uint32_t n, int root,
+                  void* stream);
+
+/* ------------------------------------------------------------------------
+ * K1/K2/K3: fused erf-soft-binned statistic.  One launch evaluates, for the
+ * local shard x[0..n), the partial per-bin sums and their parameter
+ * Jacobian, reduces them over CTAs and (if pt->world > 1) over GPUs inside
+ * the kernel, and finishes with the loss / chain rule / optimiser epilogue.
+ * Replaces OnePointModel._vjp (multigrad/multigrad.py:508-538: forward,
+ * Allreduce, dL/ds, VJP, Allreduce, second loss evaluation) and, in the
+ * optimiser modes, one iteration of _adam_optimizer (multigrad/adam.py:52-68)
+ * including the bound transforms (adam.py:172-239) or of simple_grad_descent
+ * (multigrad/util.py:100-114).
+ * ---------------------------------------------------------------------- */
+typedef struct MgbErfBinModel {
+  const float* x;        /* object coordinate (e.g. log10 halo mass) [n]     */
+  const float* w;        /* optional per-object weight [n] or NULL           */
+  int64_t n;             /* objects in this rank's shard                     */
+  int32_t nbins;         /* K <= MGB_MAX_BINS                                */
+  int32_t nparams;       /* P <= MGB_MAX_PARAMS                              */
+  int32_t mu_idx;        /* mu_h    = x_h + params[mu_idx]                   */
+  int32_t sig_idx;       /* sigma   = link(params[sig_idx])                  */
+  int32_t sigma_link;    /* 0: sigma = p, 1: sigma = 10**p                   */
+  int32_t loss_kind;     /* 0: mean (log10(s+eps)-log10(t+eps))^2
+                            1: mean (s-t)^2   2: sum ((s-t)*inv_err)^2       */
+  float loss_eps;
+  float edges[MGB_MAX_BINS + 1];
+  float norm[MGB_MAX_BINS];    /* s_k = norm_k * sum_h (Phi_{k+1}-Phi_k)     */
+  float target[MGB_MAX_BINS];
+  float inv_err[MGB_MAX_BINS];
+} MgbErfBinModel;
+
+enum {
+  MGB_MODE_SUMSTATS = 0, /* out_sumstats[B][K]                               */
+  MGB_MODE_SUMSTATS_JAC = 1, /* + out_jac[B][K][P]                           */
+  MGB_MODE_LOSS_GRAD = 2,    /* + out_loss[B], out_grad[B][P]                */
+  MGB_MODE_ADAM = 3,         /* + Adam update of the optimiser state         */
+  MGB_MODE_GD = 4            /* + fixed-step gradient-descent update         */
+};
+
+typedef struct MgbStepArgs {
+  int32_t mode;
+  int32_t batch;            /* B parameter vectors (optimiser modes: 1)      */
+  int32_t reduce;           /* 1: sum over the peer workspace, 0: local only */
+  int32_t jac_at_params;    /* bounded Adam: reference-compatible Jacobian   */
+  const float* params;      /* [B][P] evaluation points (modes 0-2)          */
+  const float* gate;        /* optional device flag: the launch is a no-op
+                               when *gate == 0 (BFGS worker pipeline)        */
+  float* out_sumstats;      /* [B][K]   or NULL                              */
+  float* out_jac;           /* [B][K][P] or NULL                             */
+  float* out_loss;          /* [B]      or NULL                              */
+  float* out_grad;          /* [B][P]   or NULL                              */
+  /* optimiser state, device resident, modes 3/4 */
+  float* opt_p;             /* [P] current (bounded) parameters              */
+  float* opt_u;             /* [P] unbounded parameters                      */
+  float* opt_m;             /* [P] */
+  float* opt_v;             /* [P] */
+  int32_t* opt_step;        /* [1] number of updates applied so far          */
+  float* traj;              /* [(nsteps+1)][P]; row step+1 is written (Adam),
+                               row step (pre-update params) for GD           */
+  float* loss_hist;         /* [nsteps]; entry step is written               */
+  int32_t traj_rows;        /* capacity of traj in rows (bounds check)       */
+  int32_t step_base;        /* row index = *opt_step - step_base (resume)    */
+  float lr, b1, b2, eps;
+  int32_t bound_kind[MGB_MAX_PARAMS]; /* 0 none 1 both 2 low-only 3 high-only */
+  float bound_lo[MGB_MAX_PARAMS];
+  float bound_hi[MGB_MAX_PARAMS];
+} MgbStepArgs;
+
+/* scratch needed by mgb_erfbin_step: bytes for `scratch` given the batch */
+uint64_t mgb_erfbin_scratch_bytes(int nbins, int batch);
+int mgb_erfbin_grid(void);
+/* `scratch` must be zero-filled once before its first use. */
+int mgb_erfbin_step(const MgbErfBinModel* model, const MgbStepArgs* args,
+                    const MgbPeerTable* pt, void* scratch,
+                    uint64_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * K3 stand-alone: Adam / bound transforms on device vectors for the generic
+ * (user-defined torch model) path.  Replaces jax_opt.adam's opt_update and
+ * the jitted per-scalar transforms (multigrad/adam.py:52-68, 192-239).
+ * ---------------------------------------------------------------------- */
+int mgb_adam_update(float* params, const float* grad, float* m, float* v,
+                    int32_t step, int32_t n, float lr, float b1, float b2,
+                    float eps, void* stream);
+
+/* ------------------------------------------------------------------------
+ * K8: pointer jumping (indices = indices[indices] to a fixed point), the
+ * device version of diffdesi_experimental.find_ultimate_top_indices
+ * (multigrad/diffdesi_experimental/util.py:18-28).  `rounds_out` receives
+ * the number of rounds; returns MGB_ESTATE if `max_rounds` is exceeded.
+ * ---------------------------------------------------------------------- */
+int mgb_pointer_jump(int64_t* indices, int64_t* tmp, int64_t n,
+                     int32_t max_rounds, int32_t* rounds_out,
+                     int32_t* changed_flag_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MULTIGRAD_B200_H_ */

@@ -1,0 +1,123 @@
+"""K6: multi-GPU L-BFGS-B with a device-side control plane.
+
+The reference drives its workers with two pickled MPI broadcasts per
+loss+gradient evaluation (``"compute"`` + params) and a final ``"exit"``
+(``multigrad/bfgs.py:72-106``).  Here the root's parameters reach the other
+GPUs by NVLink stores issued from a kernel (``mgb_bcast_f32``) and the
+workers *wait on the GPU*: each worker keeps ``DEPTH`` (hand-off, evaluation)
+kernel pairs queued, so by the time the root pushes the next point the
+worker's kernels are already resident and the evaluation starts within one
+NVLink latency.  The first float of the pushed block is a gate: 1 = evaluate,
+0 = exit (the evaluation kernel turns into a no-op).  The root sends exactly
+``DEPTH`` exit blocks so that every queued pair drains and all ranks execute
+the same number of collectives.
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.optimize
+import torch
+
+from .. import util
+from ..ops import _lib
+from ..ops.allreduce import bcast_
+
+DEPTH = 4
+
+
+def _np64(v):
+    if isinstance(v, torch.Tensor):
+        return v.detach().cpu().double().numpy()
+    return np.asarray(v, dtype=np.float64)
+
+
+def run_bfgs_device(model, guess, maxsteps, param_bounds, comm):
+    from ..ops.erfbin import MODE_LOSS_GRAD
+    plan = model.plan()
+    P = model.nparams
+    dev = model.device
+    if param_bounds is not None and hasattr(param_bounds, "tolist"):
+        param_bounds = param_bounds.tolist()
+    ctl = torch.zeros(1 + P, dtype=torch.float32, device=dev)
+    d_out = torch.zeros(1 + P, dtype=torch.float32, device=dev)
+    a = _lib.MgbStepArgs()
+    a.mode, a.batch, a.reduce = MODE_LOSS_GRAD, 1, 1
+    a.gate = ctl.data_ptr()
+    a.params = ctl.data_ptr() + 4
+    a.out_loss = d_out.data_ptr()
+    a.out_grad = d_out.data_ptr() + 4
+    stream = torch.cuda.current_stream(dev)
+
+    if comm.rank == 0:
+        h_in = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
+        h_out = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
+        pbar = util.trange(maxsteps, desc="BFGS Gradient Descent Progress",
+                           leave=True)
+
+        def fn(p):
+            h_in[0] = 1.0
+            h_in[1:] = torch.as_tensor(np.asarray(p, dtype=np.float32))
+            ctl.copy_(h_in, non_blocking=True)
+            bcast_(ctl, comm, root=0)
+            plan.launch(a)
+            h_out.copy_(d_out, non_blocking=True)
+            stream.synchronize()
+            return float(h_out[0]), h_out[1:].double().numpy().copy()
+
+        def callback(*_a, **_k):
+            if hasattr(pbar, "update"):
+                pbar.update()
+
+        result, err = None, None
+        try:
+            result = scipy.optimize.minimize(
+                fn, x0=_np64(guess).ravel(), method="L-BFGS-B", jac=True,
+                options=dict(maxiter=maxsteps), callback=callback,
+                bounds=param_bounds)
+        except BaseException as e:  # noqa: BLE001 - workers must be released
+            err = e
+        finally:
+            if hasattr(pbar, "close"):
+                pbar.close()
+            h_in.zero_()
+            for _ in range(DEPTH):
+                ctl.copy_(h_in, non_blocking=True)
+                bcast_(ctl, comm, root=0)
+                plan.launch(a)          # gated no-op, keeps launch parity
+            stream.synchronize()
+        comm.bcast(("error", repr(err)) if err is not None else
+                   ("ok", [*result.keys()], [*result.values()]), root=0)
+        if err is not None:
+            raise err
+    else:
+        flags = torch.zeros(4 * DEPTH, dtype=torch.float32).pin_memory()
+        events = []
+        launched = 0
+
+        def enqueue():
+            nonlocal launched
+            slot = launched % (4 * DEPTH)
+            bcast_(ctl, comm, root=0)
+            plan.launch(a)
+            flags[slot:slot + 1].copy_(ctl[0:1], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            events.append((ev, slot))
+            launched += 1
+
+        for _ in range(DEPTH):
+            enqueue()
+        exiting = False
+        while events:
+            ev, slot = events.pop(0)
+            ev.synchronize()
+            if not exiting and float(flags[slot]) != 0.0:
+                enqueue()
+            else:
+                exiting = True
+        msg = comm.bcast(None, root=0)
+        if msg[0] == "error":
+            raise RuntimeError(f"run_bfgs: the root rank raised {msg[1]}")
+        result = scipy.optimize.OptimizeResult(dict(zip(msg[1], msg[2])))
+    model._check_peers()
+    return result

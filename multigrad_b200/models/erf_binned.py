@@ -1,0 +1,420 @@
+"""Native model family: erf-soft-binned one-point statistics.
+
+``ErfBinnedModel`` is the B200-native counterpart of the stellar-mass-function
+models the reference ships as examples (``tests/smf_example/
+smf_grad_descent.py:17-82`` -- ``sigma = p1`` -- and ``docs/source/notebooks/
+smf_gradient_descent.py:18-91`` -- ``sigma = 10**p1``, ``+1e-10`` in the
+logs): every object ``h`` with coordinate ``x_h`` spreads a Gaussian of mean
+``mu_h = x_h + params[mu_index]`` and width ``sigma = link(params[sigma_index])``
+over the bins, and the summary statistic is the (volume- and width-normalised)
+expected count per bin.
+
+On CUDA every public method runs the fused kernel of ``csrc/erfbin.cu``: one
+launch per loss+gradient evaluation or optimiser step, with the cross-GPU
+reduction done inside the kernel over NVLink (no NCCL/MPI on the hot path).
+On CPU the same mathematics runs as differentiable PyTorch through the generic
+:class:`~multigrad_b200.core.OnePointModel` machinery, which is also the
+oracle the GPU tests compare against.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import Any, Optional
+
+import numpy as np
+import scipy.optimize
+import torch
+
+from .. import adam as _adam
+from .. import util
+from ..core import OnePointModel
+from ..ops import reference as _ref
+from ..parallel.collectives import reduce_sum
+from ..util import GradDescentResult
+
+__all__ = ["ErfBinnedModel", "SMFModel"]
+
+
+def _np(v):
+    if isinstance(v, torch.Tensor):
+        return v.detach().cpu().double().numpy()
+    return np.asarray(v, dtype=np.float64)
+
+
+@dataclass
+class ErfBinnedModel(OnePointModel):
+    """Soft-binned statistic with a shift link for the mean and a scalar
+    width.
+
+    Parameters (besides those of :class:`OnePointModel`)
+    ----------------------------------------------------
+    x : tensor, this rank's shard of object coordinates (e.g. log10 M_halo)
+    bin_edges : K+1 increasing edges
+    volume : normalisation volume (``s_k = counts_k / volume / width_k``)
+    target_sumstats : K targets for the built-in losses
+    weights : optional per-object weights
+    sigma_link : ``"identity"`` or ``"log10"``
+    loss : ``"log_mse"`` | ``"mse"`` | ``"chi2"``;  loss_eps, inv_err
+    nparams, mu_index, sigma_index : layout of the parameter vector
+
+    ``aux_data`` may carry the same information under the reference example's
+    keys (``log_halo_masses``, ``smf_bin_edges``, ``volume``,
+    ``target_sumstats``).
+    """
+    x: Any = None
+    bin_edges: Any = None
+    volume: float = 1.0
+    target_sumstats: Any = None
+    weights: Any = None
+    sigma_link: str = "identity"
+    loss: str = "log_mse"
+    loss_eps: float = 0.0
+    inv_err: Any = None
+    nparams: int = 2
+    mu_index: int = 0
+    sigma_index: int = 1
+
+    def __post_init__(self):
+        super().__post_init__()
+        aux = self.aux_data if isinstance(self.aux_data, dict) else {}
+        if self.x is None:
+            self.x = aux.get("log_halo_masses", aux.get("x"))
+        if self.bin_edges is None:
+            self.bin_edges = aux.get("smf_bin_edges", aux.get("bin_edges"))
+        if self.target_sumstats is None:
+            self.target_sumstats = aux.get("target_sumstats")
+        if "volume" in aux and self.volume == 1.0:
+            self.volume = float(aux["volume"])
+        if self.weights is None:
+            self.weights = aux.get("weights")
+        if self.x is None or self.bin_edges is None:
+            raise ValueError("ErfBinnedModel needs `x` and `bin_edges`")
+        if isinstance(self.x, torch.Tensor) and self.x.is_cuda \
+                and self.device.type != "cuda":
+            self.device = self.x.device
+        self.x = torch.as_tensor(self.x).detach().to(
+            self.device, torch.float32).contiguous()
+        if self.weights is not None:
+            self.weights = torch.as_tensor(self.weights).detach().to(
+                self.device, torch.float32).contiguous()
+        self._edges64 = _np(self.bin_edges).ravel()
+        self.nbins = self._edges64.size - 1
+        self._norm64 = 1.0 / (float(self.volume) * np.diff(self._edges64))
+        self._edges_t = torch.as_tensor(self._edges64, dtype=torch.float32,
+                                        device=self.device)
+        self._norm_t = torch.as_tensor(self._norm64, dtype=torch.float32,
+                                       device=self.device)
+        self._target_t = None
+        self._inv_err_t = None
+        self._builtin_loss = (type(self).calc_loss_from_sumstats
+                              is ErfBinnedModel.calc_loss_from_sumstats)
+        self._plan = None
+        self._host = None
+        if self.target_sumstats is not None:
+            self.set_target(self.target_sumstats, self.inv_err)
+
+    # ------------------------------------------------------------------ setup
+    @property
+    def fused(self) -> bool:
+        """True when the CUDA kernels are the execution path."""
+        return self.device.type == "cuda"
+
+    def set_target(self, target, inv_err=None) -> None:
+        """(Re)define the target summary statistics of the built-in loss."""
+        self.target_sumstats = target
+        self._target_t = torch.as_tensor(_np(target), dtype=torch.float32,
+                                         device=self.device)
+        if inv_err is not None:
+            self.inv_err = inv_err
+            self._inv_err_t = torch.as_tensor(
+                np.broadcast_to(_np(inv_err), (self.nbins,)).copy(),
+                dtype=torch.float32, device=self.device)
+        if self._plan is not None:
+            self._plan.set_target(_np(target), None if inv_err is None
+                                  else _np(inv_err))
+
+    def plan(self):
+        """The launch plan (built on first use: allocating the communicator's
+        peer workspace is a collective call)."""
+        if self._plan is None:
+            from ..ops.erfbin import ErfBinPlan
+            table = None
+            if self.comm is not None and self.comm.size > 1:
+                table = self.comm.workspace().table
+            self._plan = ErfBinPlan(
+                self.x, self._edges64, self._norm64,
+                target=None if self.target_sumstats is None
+                else _np(self.target_sumstats),
+                inv_err=None if self.inv_err is None else _np(self.inv_err),
+                nparams=self.nparams, mu_idx=self.mu_index,
+                sig_idx=self.sigma_index, sigma_link=self.sigma_link,
+                loss=self.loss, loss_eps=self.loss_eps, weights=self.weights,
+                peer_table=table)
+            self.x = self._plan.x
+        return self._plan
+
+    def _check_peers(self):
+        if self.comm is not None and self.comm.size > 1:
+            self.comm.workspace().check_error()
+
+    # --------------------------------------------------- user-hook equivalents
+    def calc_partial_sumstats_from_params(self, params, randkey=None):
+        """This rank's additive share of the binned statistic.  Differentiable
+        PyTorch when ``params`` requires grad (oracle / generic path), the
+        forward kernel otherwise."""
+        p = params if isinstance(params, torch.Tensor) else \
+            self._params(params)
+        if self.fused and not p.requires_grad:
+            from ..ops.erfbin import MODE_SUMSTATS
+            return self.plan().evaluate(p, MODE_SUMSTATS,
+                                        reduce=False)["sumstats"]
+        p = p.to(self.device)
+        return _ref.erf_binned_partial(
+            self.x.to(p.dtype), self._edges_t.to(p.dtype),
+            self._norm_t.to(p.dtype), p[self.mu_index], p[self.sigma_index],
+            self.sigma_link,
+            None if self.weights is None else self.weights.to(p.dtype))
+
+    def calc_loss_from_sumstats(self, sumstats, sumstats_aux=None,
+                                randkey=None):
+        """Built-in loss (override for a custom differentiable loss; the fused
+        path then returns sumstats + Jacobian and applies autograd to it)."""
+        if self._target_t is None:
+            raise ValueError("no target_sumstats given")
+        s = torch.as_tensor(sumstats)
+        return _ref.binned_loss(
+            s, self._target_t.to(s), self.loss, self.loss_eps,
+            None if self._inv_err_t is None else self._inv_err_t.to(s))
+
+    # ------------------------------------------------------------ fused paths
+    def calc_sumstats_from_params(self, params, total=True, randkey=None):
+        if not self.fused:
+            return super().calc_sumstats_from_params(params, total, randkey)
+        from ..ops.erfbin import MODE_SUMSTATS
+        p = self._params(params)
+        if p.dim() == 2 and total and self.comm.size > 1:
+            part = self.plan().evaluate(p, MODE_SUMSTATS, reduce=False)
+            return reduce_sum(part["sumstats"], comm=self.comm)
+        return self.plan().evaluate(p, MODE_SUMSTATS, reduce=total)["sumstats"]
+
+    def calc_sumstats_and_jac_from_params(self, params, total=True):
+        """``(s[K], ds/dp[K, P])`` in one pass (no reference counterpart: the
+        reference never materialises the Jacobian)."""
+        p = self._params(params)
+        if self.fused:
+            from ..ops.erfbin import MODE_SUMSTATS_JAC
+            out = self.plan().evaluate(p, MODE_SUMSTATS_JAC, reduce=total)
+            return out["sumstats"], out["jac"]
+        s, dmu, dsg = _ref.erf_binned_partial_and_jac(
+            self.x, self._edges_t, self._norm_t, p[self.mu_index],
+            p[self.sigma_index], self.sigma_link, self.weights)
+        jac = torch.zeros(self.nbins, self.nparams, dtype=s.dtype,
+                          device=s.device)
+        jac[:, self.mu_index] += dmu
+        jac[:, self.sigma_index] += dsg
+        if total:
+            s = reduce_sum(s, comm=self.comm)
+            jac = reduce_sum(jac, comm=self.comm)
+        return s, jac
+
+    def calc_loss_from_params(self, params, randkey=None):
+        if not self.fused:
+            return super().calc_loss_from_params(params, randkey)
+        s = self.calc_sumstats_from_params(params)
+        with torch.no_grad():
+            return self.calc_loss_from_sumstats(s)
+
+    def _vjp(self, params, randkey=None, include_loss=True):
+        if not self.fused:
+            return super()._vjp(params, randkey, include_loss)
+        from ..ops.erfbin import MODE_LOSS_GRAD, MODE_SUMSTATS_JAC
+        p = self._params(params)
+        if self._builtin_loss:
+            if self._target_t is None:
+                raise ValueError("no target_sumstats given")
+            out = self.plan().evaluate(p, MODE_LOSS_GRAD)
+            loss, grad = out["loss"], out["grad"]
+        else:
+            out = self.plan().evaluate(p, MODE_SUMSTATS_JAC)
+            kw = {} if randkey is None else {"randkey": randkey}
+            loss, dlds = self._loss_and_dloss(out["sumstats"], None, kw)
+            grad = dlds.to(out["jac"]) @ out["jac"]
+        return (loss, grad) if include_loss else grad
+
+    # --------------------------------------------------------- host fast path
+    def loss_and_grad_host(self, params_host) -> "tuple[float, np.ndarray]":
+        """Loss+gradient for host parameters with minimal host<->device
+        traffic: one pinned H2D copy of ``P`` floats, one launch, one pinned
+        D2H copy of ``1+P`` floats.  Used by ``run_bfgs`` and by the
+        end-to-end benchmark."""
+        from ..ops import _lib
+        from ..ops.erfbin import MODE_LOSS_GRAD
+        plan = self.plan()
+        if self._host is None:
+            P = self.nparams
+            h_in = torch.empty(P, dtype=torch.float32).pin_memory()
+            h_out = torch.empty(1 + P, dtype=torch.float32).pin_memory()
+            d_in = torch.empty(P, dtype=torch.float32, device=self.device)
+            d_out = torch.empty(1 + P, dtype=torch.float32,
+                                device=self.device)
+            a = _lib.MgbStepArgs()
+            a.mode, a.batch = MODE_LOSS_GRAD, 1
+            a.reduce = 1 if plan.world > 1 else 0
+            a.params = d_in.data_ptr()
+            a.out_loss = d_out.data_ptr()
+            a.out_grad = d_out.data_ptr() + 4
+            self._host = (h_in, h_out, d_in, d_out, a)
+        h_in, h_out, d_in, d_out, a = self._host
+        h_in.copy_(torch.as_tensor(np.asarray(params_host, dtype=np.float32)))
+        d_in.copy_(h_in, non_blocking=True)
+        plan.launch(a)
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(h_out[0]), h_out[1:].double().numpy().copy()
+
+    # -------------------------------------------------------------- optimisers
+    def run_adam(self, guess, nsteps=100, param_bounds=None,
+                 learning_rate=0.01, randkey=None, const_randkey=False,
+                 comm=None, reference_compat=True, init_state=None,
+                 return_state=False, return_loss=False, use_graph=None):
+        """Adam with one fused kernel launch per step (``csrc/erfbin.cu``
+        mode 3): sumstats + Jacobian + NVLink all-reduce + loss + chain rule +
+        bound transforms + update, trajectory and loss history written on the
+        device.  Same return convention as :meth:`OnePointModel.run_adam`."""
+        if not (self.fused and self._builtin_loss):
+            return super().run_adam(
+                guess, nsteps, param_bounds, learning_rate, randkey,
+                const_randkey, comm, reference_compat, init_state,
+                return_state, return_loss)
+        from ..ops.erfbin import FitState, MODE_ADAM
+        plan = self.plan()
+        p0 = self._params(guess)
+        bounds = None
+        u0 = p0
+        if param_bounds is not None:
+            bounds = _adam.normalize_bounds(param_bounds, p0.numel())
+            u0 = _adam.apply_transforms(p0.cpu(), bounds).to(self.device)
+        step0, m, v = 0, None, None
+        if init_state is not None:
+            step0, m, v = int(init_state.step), init_state.m, init_state.v
+        st = FitState(p0, u0, nsteps, self.device, step0=step0, m=m, v=v)
+        st.traj[0].copy_(p0)
+        args = plan.make_optimizer_args(
+            MODE_ADAM, st, learning_rate, bounds,
+            jac_at_params=reference_compat)
+        self._run_steps(plan, args, nsteps, use_graph)
+        self._check_peers()
+        out = [st.traj]
+        if return_loss:
+            out.append(st.loss_hist[:nsteps])
+        if return_state:
+            out.append(_adam.AdamState(step0 + nsteps, st.m, st.v))
+        return out[0] if len(out) == 1 else tuple(out)
+
+    def run_simple_grad_descent(self, guess, nsteps=100, learning_rate=0.01,
+                                use_graph=None):
+        """Fixed-step gradient descent, one fused launch per step (mode 4).
+        Records pre-update params like the reference (quirk Q6)."""
+        if not (self.fused and self._builtin_loss):
+            return super().run_simple_grad_descent(guess, nsteps,
+                                                   learning_rate)
+        from ..ops.erfbin import FitState, MODE_GD
+        plan = self.plan()
+        p0 = self._params(guess)
+        st = FitState(p0, p0, nsteps, self.device, rows=max(nsteps, 1))
+        args = plan.make_optimizer_args(MODE_GD, st, learning_rate)
+        self._run_steps(plan, args, nsteps, use_graph)
+        self._check_peers()
+        return GradDescentResult(loss=st.loss_hist[:nsteps],
+                                 params=st.traj[:nsteps],
+                                 aux=[None] * nsteps)
+
+    def _run_steps(self, plan, args, nsteps: int, use_graph) -> None:
+        """Issue ``nsteps`` fused step launches, optionally as replays of a
+        captured CUDA graph (the step index and the collective epoch live on
+        the device, so a replay is a valid continuation)."""
+        if use_graph is None:
+            use_graph = os.environ.get("MULTIGRAD_B200_GRAPH", "0") == "1"
+        chunk = int(os.environ.get("MULTIGRAD_B200_GRAPH_CHUNK", "50"))
+        done = 0
+        if use_graph and nsteps >= 2 * chunk:
+            # warm-up launch outside capture, then capture `chunk` launches
+            plan.launch(args)
+            done = 1
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(chunk):
+                    plan.launch(args)
+            done += chunk      # capture does not execute: replay once now
+            g.replay()
+            while nsteps - done >= chunk:
+                g.replay()
+                done += chunk
+            self._graph = g    # keep alive until the stream drains
+        for _ in range(nsteps - done):
+            plan.launch(args)
+
+    def run_bfgs(self, guess, maxsteps=100, param_bounds=None, randkey=None,
+                 comm=None):
+        """L-BFGS-B on the host of rank 0 with one fused loss+gradient launch
+        per line-search evaluation.  With several GPUs the parameters are
+        handed to the workers by a device-side push (``mgb_bcast_f32``) and
+        the workers wait on the GPU: no host message per evaluation."""
+        if not (self.fused and self._builtin_loss):
+            return super().run_bfgs(guess, maxsteps, param_bounds, randkey,
+                                    comm)
+        comm = self.comm if comm is None else comm
+        if comm is not None and comm.size > 1:
+            from .bfgs_device import run_bfgs_device
+            return run_bfgs_device(self, guess, maxsteps, param_bounds, comm)
+        if param_bounds is not None and hasattr(param_bounds, "tolist"):
+            param_bounds = param_bounds.tolist()
+        x0 = _np(guess).ravel()
+        pbar = util.trange(maxsteps, desc="BFGS Gradient Descent Progress",
+                           leave=True)
+
+        def callback(*_a, **_k):
+            if hasattr(pbar, "update"):
+                pbar.update()
+        try:
+            return scipy.optimize.minimize(
+                self.loss_and_grad_host, x0=x0, method="L-BFGS-B", jac=True,
+                options=dict(maxiter=maxsteps), callback=callback,
+                bounds=param_bounds)
+        finally:
+            if hasattr(pbar, "close"):
+                pbar.close()
+
+    def run_lhs_param_scan(self, xmins, xmaxs, n_dim, num_evaluations,
+                           seed=None, randkey=None):
+        """Latin-hypercube scan with **all draws evaluated in one launch**
+        (batched forward kernel) instead of a host loop."""
+        if not self.fused:
+            return super().run_lhs_param_scan(xmins, xmaxs, n_dim,
+                                              num_evaluations, seed, randkey)
+        params = util.latin_hypercube_sampler(xmins, xmaxs, n_dim,
+                                              num_evaluations, seed=seed)
+        from ..ops._lib import MGB_MAX_BATCH
+        p = torch.as_tensor(params, dtype=torch.float32, device=self.device)
+        chunks = []
+        for lo in range(0, p.shape[0], MGB_MAX_BATCH):
+            chunks.append(self.calc_sumstats_from_params(
+                p[lo:lo + MGB_MAX_BATCH].contiguous()))
+        sumstats = torch.cat(chunks) if chunks else torch.zeros(
+            0, self.nbins, device=self.device)
+        with torch.no_grad():
+            losses = torch.stack([self.calc_loss_from_sumstats(s)
+                                  for s in sumstats]) \
+                if len(sumstats) else torch.zeros(0)
+        return params, sumstats.cpu().numpy(), losses.cpu().numpy()
+
+
+@dataclass
+class SMFModel(ErfBinnedModel):
+    """Stellar-mass-function model of the reference examples.
+
+    ``params = (log_shmrat, sigma_logsm)`` (``sigma_link="identity"``, the
+    test-suite model) or ``(log_f, log_sigma)`` with ``sigma_link="log10"``
+    and ``loss_eps=1e-10`` (the tutorial model)."""
+    pass
