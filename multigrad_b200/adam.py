@@ -210,14 +210,20 @@ def inverse_transform_jacobian_diag(x, bounds):
     return torch.ones_like(x)
 
 
+def _as_tensor_keepgrad(x):
+    if isinstance(x, torch.Tensor):
+        return x if x.is_floating_point() else x.to(torch.float32)
+    return torch.as_tensor(np.asarray(x, dtype=np.float32))
+
+
 def apply_transforms(params, bounds):
-    params = _as_params(params)
+    params = _as_tensor_keepgrad(params)
     return torch.stack([transform(params[..., i], b)
                         for i, b in enumerate(bounds)], dim=-1)
 
 
 def apply_inverse_transforms(uparams, bounds):
-    uparams = _as_params(uparams)
+    uparams = _as_tensor_keepgrad(uparams)
     return torch.stack([inverse_transform(uparams[..., i], b)
                         for i, b in enumerate(bounds)], dim=-1)
 

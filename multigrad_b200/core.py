@@ -51,7 +51,7 @@ def _as_params(params, device=None, dtype=torch.float32) -> torch.Tensor:
     return p
 
 
-@dataclass
+@dataclass(eq=False)
 class OnePointModel:
     """Data-parallel differentiable one-point model (abstract).
 
@@ -270,7 +270,7 @@ def _model_comm(obj):
     return obj.main_comm if isinstance(obj, OnePointGroup) else obj.comm
 
 
-@dataclass
+@dataclass(eq=False)
 class OnePointGroup:
     """Several :class:`OnePointModel` s evaluated at the same parameters on
     disjoint sub-communicators; losses and gradients are summed (reference

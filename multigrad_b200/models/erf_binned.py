@@ -42,7 +42,7 @@ def _np(v):
     return np.asarray(v, dtype=np.float64)
 
 
-@dataclass
+@dataclass(eq=False)
 class ErfBinnedModel(OnePointModel):
     """Soft-binned statistic with a shift link for the mean and a scalar
     width.
@@ -410,7 +410,7 @@ class ErfBinnedModel(OnePointModel):
         return params, sumstats.cpu().numpy(), losses.cpu().numpy()
 
 
-@dataclass
+@dataclass(eq=False)
 class SMFModel(ErfBinnedModel):
     """Stellar-mass-function model of the reference examples.
 

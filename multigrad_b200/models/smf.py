@@ -95,7 +95,7 @@ def calc_smf_bin(params, logsm_low, logsm_high, volume, log_halo_masses):
     return torch.sum(cdf_high - cdf_low) / volume / (logsm_high - logsm_low)
 
 
-@dataclass
+@dataclass(eq=False)
 class MySMFModel(OnePointModel):
     """User-style model: two differentiable torch hooks, nothing else."""
     aux_data: dict = None
@@ -119,7 +119,7 @@ class MySMFModel(OnePointModel):
         return torch.mean((torch.log10(sumstats) - target) ** 2)
 
 
-@dataclass
+@dataclass(eq=False)
 class TutorialSMFModel(MySMFModel):
     """Tutorial variant: ``sigma = 10**log_sigma`` and ``+1e-10`` inside the
     logs (reference ``docs/.../smf_gradient_descent.py:21-35,86-91``)."""

@@ -163,7 +163,7 @@ class Comm:
     def Allreduce(self, sendbuf, recvbuf=None, op: str = "sum"):
         """Sum a host buffer over ranks (gloo).  ``recvbuf`` is filled in
         place when given (mpi4py upper-case semantics) and also returned."""
-        arr = np.ascontiguousarray(np.asarray(sendbuf))
+        arr = _c_array(sendbuf)
         if self.size > 1:
             t = torch.from_numpy(arr.copy())
             if t.dtype == torch.bool:
@@ -175,7 +175,7 @@ class Comm:
         return arr
 
     def Reduce(self, sendbuf, recvbuf=None, op: str = "sum", root: int = 0):
-        arr = np.ascontiguousarray(np.asarray(sendbuf))
+        arr = _c_array(sendbuf)
         if self.size > 1:
             t = torch.from_numpy(arr.copy())
             dist.reduce(t, dst=self._ranks[root], op=_op(op),
@@ -228,6 +228,13 @@ class Comm:
             from .workspace import PeerWorkspace
             self._workspace = PeerWorkspace(self)
         return self._workspace
+
+
+def _c_array(buf) -> np.ndarray:
+    """C-contiguous view/copy that keeps 0-d shapes (``ascontiguousarray``
+    would promote scalars to 1-d)."""
+    arr = np.asarray(buf)
+    return np.ascontiguousarray(arr).reshape(arr.shape)
 
 
 def _op(op):

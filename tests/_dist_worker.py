@@ -1,0 +1,253 @@
+"""Multi-rank test body, run under torchrun by test_distributed_cpu.py (gloo,
+CPU) and test_multigpu.py (one rank per GPU).  Every case runs on every rank;
+rank 0 prints ``RESULT {case: "ok" | "<error>"}``.
+
+Mirrors how the reference tests multi-process behaviour: the same assertions
+under real multi-process launches of different sizes (reference
+``tests/test_mpi.py:1-7``), never a mocked communicator.
+"""
+import json
+import os
+import sys
+import traceback
+
+import numpy as np
+import torch
+
+import multigrad_b200 as mg
+from multigrad_b200 import adam
+from multigrad_b200.models import smf, SMFModel
+from multigrad_b200.parallel import group_assignment
+
+COMM = mg.COMM
+RANK, SIZE = COMM.rank, COMM.size
+DEV = mg.parallel.local_device()
+CASES = {}
+
+
+def case(fn):
+    CASES[fn.__name__] = fn
+    return fn
+
+
+@case
+def reduce_sum_scalar_and_array():
+    # reference tests/test_mpi.py:19-35
+    expected = sum(range(SIZE))
+    assert mg.reduce_sum(torch.tensor(RANK)) == expected
+    assert mg.reduce_sum(float(RANK)) == float(expected)
+    out = mg.reduce_sum(np.full(3, RANK, dtype=np.float64))
+    assert isinstance(out, np.ndarray) and np.all(out == expected)
+    t = mg.reduce_sum(torch.full((5,), float(RANK), device=DEV))
+    assert t.device.type == DEV.type and torch.all(t == expected)
+    gathered = COMM.allgather(float(t[0]))
+    assert all(x == expected for x in gathered)
+    r = mg.reduce_sum(np.ones(2) * RANK, root=SIZE - 1)
+    if RANK == SIZE - 1:
+        assert np.all(r == expected)
+    else:
+        assert np.all(r == 0)           # Q7: zeros, not uninitialised memory
+
+
+@case
+def comm_object_collectives():
+    assert COMM.bcast({"a": RANK} if RANK == 0 else None, root=0) == {"a": 0}
+    assert COMM.allgather(RANK) == list(range(SIZE))
+    COMM.Barrier()
+    if SIZE > 1:
+        if RANK == 0:
+            COMM.send(np.arange(3), dest=1)
+        elif RANK == 1:
+            assert np.array_equal(COMM.recv(source=0), np.arange(3))
+    assert COMM.Get_rank() == RANK and COMM.Get_size() == SIZE
+    assert mg.RANK == RANK and mg.N_RANKS == SIZE
+
+
+@case
+def scatter_nd_chunks():
+    full = np.arange(7 * 3, dtype=np.float32).reshape(7, 3)
+    mine = mg.util.scatter_nd(full if RANK == 0 else None, axis=0, root=0)
+    want = np.array_split(full, SIZE, axis=0)[RANK]
+    assert np.array_equal(np.asarray(mine), want)
+    cols = mg.scatter_nd(full if RANK == 0 else None, axis=1)
+    assert np.array_equal(np.asarray(cols),
+                          np.array_split(full, SIZE, axis=1)[RANK])
+
+
+@case
+def split_subcomms_mapping():
+    if SIZE < 2:
+        return
+    sub, n, g = mg.split_subcomms(num_groups=2)
+    table, _ = group_assignment(SIZE, 2)
+    assert n == 2 and g == table[RANK]
+    assert sub.size == table.count(g)
+    assert sub.rank == table[:RANK].count(g)
+    assert mg.reduce_sum(1.0, comm=sub) == float(sub.size)
+    rpg = [1, SIZE - 1]
+    sub2, n2, g2 = mg.split_subcomms(ranks_per_group=rpg)
+    assert n2 == 2 and g2 == (0 if RANK == 0 else 1)
+    assert sub2.size == rpg[g2]
+    node, n_nodes, idx = mg.split_subcomms_by_node()
+    assert n_nodes == 1 and idx == 0 and node.size == SIZE
+    for bad in (dict(), dict(num_groups=2, ranks_per_group=rpg),
+                dict(num_groups=SIZE + 1), dict(ranks_per_group=[SIZE + 3])):
+        try:
+            mg.split_subcomms(**bad)
+        except AssertionError:
+            continue
+        raise AssertionError(f"split_subcomms({bad}) should have asserted")
+
+
+def _data(n):
+    return smf.make_smf_data(n, comm=COMM, device=DEV)
+
+
+def _pipeline(model, data):
+    # reference tests/test_mpi.py:38-66 (world-size invariant constants)
+    truth = smf.ParamTuple(log_shmrat=-2.0, sigma_logsm=0.2)
+    s = model.calc_sumstats_from_params(truth)
+    assert torch.allclose(data["target_sumstats"].cpu(), s.cpu()), s
+    gd = model.run_simple_grad_descent(guess=truth, nsteps=2)
+    assert torch.isclose(gd.loss[-1].cpu(), torch.tensor(0.0))
+    assert torch.allclose(gd.params[-1].cpu(), torch.tensor([*truth]))
+    assert torch.allclose(model.calc_dloss_dparams(truth).cpu(),
+                          torch.zeros(2), atol=1e-4)
+    loss, grad = model.calc_loss_and_grad_from_params(truth)
+    assert torch.allclose(loss, model.calc_loss_from_params(truth))
+    assert torch.allclose(grad, model.calc_dloss_dparams(truth), atol=1e-6)
+
+
+@case
+def pipeline_generic():
+    data = _data(10_000)
+    _pipeline(smf.MySMFModel(aux_data=data), data)
+
+
+@case
+def pipeline_native():
+    data = _data(10_000)
+    _pipeline(SMFModel(aux_data=data), data)
+
+
+@case
+def world_size_invariance():
+    """loss / grad / Adam trajectory equal the single-process values."""
+    data = _data(6_000)
+    model = SMFModel(aux_data=data)
+    full = smf.make_smf_data(6_000, comm=mg.Comm(None), device="cpu")
+    ref = SMFModel(aux_data=full, comm=mg.Comm(None), device="cpu")
+    p = torch.tensor([-1.9, 0.3])
+    loss, grad = model.calc_loss_and_grad_from_params(p)
+    rl, rg = ref.calc_loss_and_grad_from_params(p)
+    assert torch.allclose(loss.cpu(), rl, rtol=2e-5), (loss, rl)
+    assert torch.allclose(grad.cpu(), rg, rtol=2e-4, atol=1e-6), (grad, rg)
+    traj = model.run_adam(p, nsteps=8, learning_rate=0.02)
+    rt = ref.run_adam(p, nsteps=8, learning_rate=0.02)
+    assert traj.shape == (9, 2)
+    assert torch.allclose(traj.cpu(), rt, atol=2e-4), (traj, rt)
+    # identical on every rank, bit for bit
+    all_t = COMM.allgather(traj.cpu().numpy().tobytes())
+    assert all(t == all_t[0] for t in all_t)
+    tb = model.run_adam(p, nsteps=8, learning_rate=0.02,
+                        param_bounds=[(-5.0, 0.0), (0.01, None)])
+    rb = ref.run_adam(p, nsteps=8, learning_rate=0.02,
+                      param_bounds=[(-5.0, 0.0), (0.01, None)])
+    assert torch.allclose(tb.cpu(), rb, atol=2e-4), (tb, rb)
+
+
+@case
+def bfgs_all_ranks_same_result():
+    x = torch.log10(smf.load_halo_masses_tutorial(10_000, comm=COMM)).to(DEV)
+    edges = torch.linspace(9, 10, 11)
+    true = torch.tensor([-2.0, -0.5])
+    model = SMFModel(x=x, bin_edges=edges, volume=1.0, sigma_link="log10",
+                     loss_eps=1e-10, target_sumstats=torch.ones(10))
+    model.set_target(model.calc_sumstats_from_params(true))
+    res = model.run_bfgs(true + torch.tensor([-1.5, 0.7]))
+    assert res.success and np.allclose(res.x, [-2.0, -0.5], atol=2e-4), res
+    xs = COMM.allgather(np.asarray(res.x).tobytes())
+    assert all(v == xs[0] for v in xs)
+    assert res.nit >= 5 and res.nfev >= res.nit
+    gen = smf.TutorialSMFModel(aux_data=dict(
+        log_halo_masses=x, smf_bin_edges=edges.to(DEV), volume=1.0,
+        target_sumstats=model.target_sumstats))
+    res2 = gen.run_bfgs(true + torch.tensor([-1.5, 0.7]))
+    assert np.allclose(res2.x, [-2.0, -0.5], atol=2e-4), res2
+
+
+@case
+def group_of_models():
+    """OnePointGroup over disjoint sub-communicators == sum of the models
+    evaluated on all the data (config W4: multi-redshift SMF)."""
+    if SIZE < 2:
+        return
+    vols = [1.0, 1.7]
+    sub, n, g = mg.split_subcomms(num_groups=2)
+    full = smf.make_smf_data(4_000, comm=mg.Comm(None), device="cpu")
+    x_full = full["log_halo_masses"] + 0.05 * g     # "redshift" dependent
+    x_mine = torch.tensor_split(x_full, sub.size)[sub.rank].to(DEV)
+    mine = SMFModel(x=x_mine, bin_edges=full["smf_bin_edges"],
+                    volume=full["volume"] * vols[g],
+                    target_sumstats=full["target_sumstats"], comm=sub)
+    group = mg.OnePointGroup((mine,), main_comm=COMM)
+    p = torch.tensor([-1.95, 0.25])
+    loss, grad = group.calc_loss_and_grad_from_params(p)
+    rl, rg = 0.0, torch.zeros(2)
+    for gi in range(2):
+        ref = SMFModel(x=full["log_halo_masses"] + 0.05 * gi,
+                       bin_edges=full["smf_bin_edges"],
+                       volume=full["volume"] * vols[gi],
+                       target_sumstats=full["target_sumstats"],
+                       comm=mg.Comm(None), device="cpu")
+        a, b = ref.calc_loss_and_grad_from_params(p)
+        rl, rg = rl + a, rg + b
+    assert torch.allclose(loss.cpu(), rl, rtol=2e-5), (loss, rl)
+    assert torch.allclose(grad.cpu(), rg, rtol=2e-4, atol=1e-6), (grad, rg)
+    traj = group.run_adam(p, nsteps=4, learning_rate=0.01)
+    assert traj.shape == (5, 2)
+    ts = COMM.allgather(traj.cpu().numpy().tobytes())
+    assert all(t == ts[0] for t in ts)
+    res = group.run_bfgs(p, maxsteps=5)
+    assert np.all(np.isfinite(res.x))
+
+
+@case
+def experimental_scan_gd():
+    from multigrad_b200.experimental import scan_gd
+    data = torch.arange(10, dtype=torch.float32)
+    mine = scan_gd.distribute_data(data)
+    lens = COMM.allgather(len(mine))
+    assert sum(lens) == 10
+    tot = scan_gd.reduce_sum(torch.tensor([float(RANK)], device=DEV))
+    assert float(tot) == sum(range(SIZE))
+
+    def loss_and_grad(d, params):
+        x = d["x"].to(params)
+        r = params[0] * x - 2.0 * x
+        return (r * r).sum(), (2 * r * x).sum().reshape(1)
+    df = scan_gd.simple_grad_descent(
+        {"x": mine.to(DEV)}, loss_and_grad, torch.zeros(1, device=DEV),
+        learning_rate=1e-3, nsteps=50)
+    assert len(df) == 50 and abs(df["params"].iloc[-1][0] - 2.0) < 0.05
+
+
+def main():
+    only = sys.argv[1:] or list(CASES)
+    results = {}
+    for name in only:
+        try:
+            CASES[name]()
+            msg = "ok"
+        except BaseException:  # noqa: BLE001
+            msg = traceback.format_exc()[-1500:]
+        all_msgs = COMM.allgather(msg)
+        bad = [f"rank {r}: {m}" for r, m in enumerate(all_msgs) if m != "ok"]
+        results[name] = "ok" if not bad else "\n".join(bad)
+    if RANK == 0:
+        print("RESULT " + json.dumps(results), flush=True)
+    mg.shutdown()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,341 @@
+"""GPU numerics: every CUDA kernel against a plain PyTorch reference of the
+same op (float64 oracle on the same float32 inputs, plus the generic
+autograd path).  All tests need one B200."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import multigrad_b200 as mg
+from multigrad_b200 import adam
+from multigrad_b200.models import smf, SMFModel, ErfBinnedModel
+from multigrad_b200.ops import reference as ref
+
+pytestmark = pytest.mark.gpu
+
+SELF = mg.Comm(None)
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+def oracle(x, edges, norm, p, link="identity", weights=None):
+    """float64 (s, ds/dmu, ds/dsig) on the float32 inputs."""
+    x64 = x.double().cpu()
+    e64 = torch.as_tensor(np.asarray(edges, dtype=np.float32)).double()
+    n64 = torch.as_tensor(np.asarray(norm, dtype=np.float32)).double()
+    w64 = None if weights is None else weights.double().cpu()
+    p64 = torch.as_tensor(np.asarray(p, dtype=np.float32)).double()
+    return ref.erf_binned_partial_and_jac(x64, e64, n64, p64[0], p64[1], link,
+                                          w64)
+
+
+def make(n=20_000, k=10, link="identity", weights=False, seed=0, lo=9.0,
+         hi=10.0, **kw):
+    g = torch.Generator().manual_seed(seed)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    edges = np.linspace(lo, hi, k + 1)
+    w = torch.rand(n, generator=g).float() + 0.5 if weights else None
+    m = ErfBinnedModel(x=x.to(dev()), bin_edges=edges,
+                       volume=10.0 * max(n, 1),
+                       weights=None if w is None else w.to(dev()),
+                       sigma_link=link, comm=SELF, device=dev(), **kw)
+    return m, x, w, edges
+
+
+@pytest.mark.parametrize("k", [1, 2, 7, 10, 16, 17, 23, 32])
+def test_sumstats_and_jacobian_vs_fp64(k):
+    m, x, w, edges = make(k=k)
+    p = [-1.9, 0.3]
+    s, jac = m.calc_sumstats_and_jac_from_params(p)
+    so, dmu, dsg = oracle(x, edges, m._norm64, p)
+    assert s.shape == (k,) and jac.shape == (k, 2)
+    assert torch.allclose(s.double().cpu(), so, rtol=3e-6, atol=1e-12)
+    scale = max(dmu.abs().max(), dsg.abs().max())
+    assert torch.allclose(jac[:, 0].double().cpu(), dmu, rtol=1e-5,
+                          atol=3e-6 * float(scale))
+    assert torch.allclose(jac[:, 1].double().cpu(), dsg, rtol=1e-5,
+                          atol=3e-6 * float(scale))
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 1023, 4097, 100_003])
+def test_ragged_sizes(n):
+    m, x, w, edges = make(n=max(n, 0), k=5)
+    p = [-2.0, 0.2]
+    s = m.calc_sumstats_from_params(p)
+    so, _, _ = oracle(x, edges, m._norm64, p)
+    assert torch.allclose(s.double().cpu(), so, rtol=3e-6, atol=1e-12)
+
+
+def test_weights_and_log10_link():
+    m, x, w, edges = make(k=10, link="log10", weights=True)
+    p = [-2.1, -0.6]
+    s, jac = m.calc_sumstats_and_jac_from_params(p)
+    so, dmu, dsg = oracle(x, edges, m._norm64, p, "log10", w)
+    assert torch.allclose(s.double().cpu(), so, rtol=3e-6)
+    assert torch.allclose(jac[:, 0].double().cpu(), dmu, rtol=2e-5,
+                          atol=3e-6 * float(dmu.abs().max()))
+    assert torch.allclose(jac[:, 1].double().cpu(), dsg, rtol=2e-5,
+                          atol=3e-6 * float(dsg.abs().max()))
+
+
+def test_tail_accuracy_far_from_bins():
+    """Objects many sigma away from every bin: the kernel keeps relative
+    accuracy where erf-based differences lose it completely."""
+    n = 4096
+    x = torch.full((n,), 10.0)
+    edges = np.linspace(11.0, 12.0, 6)          # bins 5..10 sigma above mu
+    m = ErfBinnedModel(x=x.to(dev()), bin_edges=edges, volume=1.0,
+                       comm=SELF, device=dev())
+    p = [0.0, 0.2]
+    s = m.calc_sumstats_from_params(p).double().cpu()
+    so, _, _ = oracle(x, edges, m._norm64, p)
+    assert so[0] > 0 and so[0] < 1e-2
+    good = so > 1e-30
+    assert torch.allclose(s[good], so[good], rtol=2e-5)
+
+
+def test_parameter_layout_and_batch():
+    m, x, w, edges = make(k=6, nparams=5, mu_index=3, sigma_index=1)
+    P = torch.tensor([[0.0, 0.3, 7.0, -1.9, 5.0],
+                      [1.0, 0.25, 0.0, -2.0, 0.0],
+                      [2.0, 0.5, 0.0, -1.5, 0.0]])
+    S = m.calc_sumstats_from_params(P)
+    assert S.shape == (3, 6)
+    for i in range(3):
+        so, dmu, dsg = oracle(x, edges, m._norm64, [P[i, 3], P[i, 1]])
+        assert torch.allclose(S[i].double().cpu(), so, rtol=3e-6)
+    s, jac = m.calc_sumstats_and_jac_from_params(P[0])
+    assert jac.shape == (6, 5)
+    assert torch.all(jac[:, [0, 2, 4]] == 0)
+    _, dmu0, dsg0 = oracle(x, edges, m._norm64, [P[0, 3], P[0, 1]])
+    assert torch.allclose(jac[:, 3].double().cpu(), dmu0, rtol=1e-5,
+                          atol=3e-6 * float(dmu0.abs().max()))
+    assert torch.allclose(jac[:, 1].double().cpu(), dsg0, rtol=1e-5,
+                          atol=3e-6 * float(dsg0.abs().max()))
+
+
+@pytest.mark.parametrize("loss,eps", [("log_mse", 0.0), ("log_mse", 1e-10),
+                                      ("mse", 0.0), ("chi2", 0.0)])
+def test_loss_and_grad_vs_autograd(loss, eps):
+    m, x, w, edges = make(k=10, loss=loss, loss_eps=eps,
+                          inv_err=np.linspace(50, 500, 10))
+    truth = [-2.0, 0.2]
+    m.set_target(m.calc_sumstats_from_params(truth), m.inv_err)
+    p = torch.tensor([-1.93, 0.27])
+    lval, g = m.calc_loss_and_grad_from_params(p)
+    # float64 autograd of the same op
+    cpu = ErfBinnedModel(x=x.double(), bin_edges=edges, volume=m.volume,
+                         comm=SELF, device="cpu", loss=loss, loss_eps=eps,
+                         inv_err=np.linspace(50, 500, 10),
+                         target_sumstats=m._target_t.cpu())
+    p64 = p.double().requires_grad_(True)
+    s64 = ref.erf_binned_partial(x.double(), cpu._edges_t.double(),
+                                 cpu._norm_t.double(), p64[0], p64[1])
+    l64 = ref.binned_loss(s64, m._target_t.cpu().double(), loss, eps,
+                          cpu._inv_err_t.double())
+    (g64,) = torch.autograd.grad(l64, p64)
+    assert math.isclose(float(lval), float(l64), rel_tol=2e-4, abs_tol=1e-12)
+    assert torch.allclose(g.double().cpu(), g64, rtol=5e-4,
+                          atol=1e-5 * float(g64.abs().max()))
+    assert torch.allclose(m.calc_dloss_dparams(p), g)
+    assert torch.allclose(m.calc_loss_from_params(p), lval, rtol=1e-5)
+
+
+def test_reference_test_constants_on_gpu():
+    # reference tests/test_mpi.py:38-66 through the fused kernels
+    data = smf.make_smf_data(10_000, comm=SELF, device=dev())
+    model = SMFModel(aux_data=data, comm=SELF, device=dev())
+    truth = smf.ParamTuple()
+    s = model.calc_sumstats_from_params(truth)
+    assert torch.allclose(data["target_sumstats"], s)
+    gd = model.run_simple_grad_descent(guess=truth, nsteps=2)
+    assert gd.loss.shape == (2,) and gd.params.shape == (2, 2)
+    assert torch.isclose(gd.loss[-1].cpu(), torch.tensor(0.0))
+    assert torch.allclose(gd.params[-1].cpu(), torch.tensor([*truth]))
+    assert torch.allclose(gd.params[0].cpu(), torch.tensor([*truth]))
+    assert torch.allclose(model.calc_dloss_dparams(truth).cpu(),
+                          torch.zeros(2), atol=1e-4)
+
+
+def _cpu_twin(model, x):
+    return ErfBinnedModel(
+        x=x, bin_edges=model._edges64, volume=model.volume,
+        target_sumstats=model._target_t.cpu(), sigma_link=model.sigma_link,
+        loss=model.loss, loss_eps=model.loss_eps, comm=SELF, device="cpu")
+
+
+@pytest.mark.parametrize("bounds", [None, [(-5.0, 0.0), (0.01, None)],
+                                    [(None, -1.0), None]])
+@pytest.mark.parametrize("compat", [True, False])
+def test_fused_adam_trajectory_matches_generic(bounds, compat):
+    m, x, w, edges = make(n=30_000, k=10)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    twin = _cpu_twin(m, x)
+    guess = [-1.7, 0.35]
+    kw = dict(nsteps=25, learning_rate=0.02, param_bounds=bounds,
+              reference_compat=compat)
+    traj, losses, state = m.run_adam(guess, return_loss=True,
+                                     return_state=True, **kw)
+    rt, rl, rstate = twin.run_adam(guess, return_loss=True,
+                                   return_state=True, **kw)
+    assert traj.shape == (26, 2) and losses.shape == (25,)
+    assert torch.allclose(traj.cpu(), rt, atol=3e-4), (traj[-1], rt[-1])
+    assert torch.allclose(losses.cpu(), rl, rtol=2e-3, atol=1e-7)
+    assert state.step == 25
+    assert torch.allclose(state.m.cpu(), rstate.m, rtol=1e-2, atol=1e-5)
+    # resume continues the same trajectory
+    t2 = m.run_adam(traj[-1], nsteps=5, learning_rate=0.02,
+                    param_bounds=bounds, reference_compat=compat,
+                    init_state=state)
+    full = m.run_adam(guess, nsteps=30, learning_rate=0.02,
+                      param_bounds=bounds, reference_compat=compat)
+    assert torch.allclose(t2[-1], full[-1], atol=2e-5)
+
+
+def test_fused_adam_cuda_graph_equals_stream_launches():
+    m, x, w, edges = make(n=20_000, k=10)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    a = m.run_adam([-1.7, 0.35], nsteps=130, learning_rate=0.01,
+                   use_graph=False)
+    b = m.run_adam([-1.7, 0.35], nsteps=130, learning_rate=0.01,
+                   use_graph=True)
+    assert torch.equal(a, b)            # deterministic reduction order
+
+
+def test_fused_gd_matches_generic():
+    m, x, w, edges = make(n=10_000, k=10)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    twin = _cpu_twin(m, x)
+    r = m.run_simple_grad_descent([-1.9, 0.25], nsteps=10, learning_rate=0.01)
+    rr = twin.run_simple_grad_descent([-1.9, 0.25], nsteps=10,
+                                      learning_rate=0.01)
+    assert torch.allclose(r.params.cpu(), rr.params, atol=1e-4)
+    assert torch.allclose(r.loss.cpu(), rr.loss, rtol=2e-3, atol=1e-8)
+
+
+def test_bfgs_tutorial_on_gpu():
+    # docs/source/notebooks/intro.ipynb:258-281 through the fused kernel
+    x = torch.log10(smf.load_halo_masses_tutorial(10_000, comm=SELF))
+    true = torch.tensor([-2.0, -0.5])
+    m = SMFModel(x=x.to(dev()), bin_edges=np.linspace(9, 10, 11), volume=1.0,
+                 sigma_link="log10", loss_eps=1e-10, comm=SELF, device=dev(),
+                 target_sumstats=torch.ones(10))
+    m.set_target(m.calc_sumstats_from_params(true))
+    loss, grad = m.calc_loss_and_grad_from_params(true + 0.1)
+    assert abs(float(loss) - 0.44032094) < 3e-5
+    assert np.allclose(grad.cpu().numpy(), [2.6187496, 4.2603974], rtol=5e-5)
+    res = m.run_bfgs(true + torch.tensor([-1.5, 0.7]))
+    assert res.success and res.fun < 1e-9
+    assert np.allclose(res.x, [-2.0, -0.5], atol=2e-4)
+    assert 10 <= res.nit <= 25
+    l, g = m.loss_and_grad_host([-1.9, -0.4])
+    assert abs(l - 0.44032094) < 3e-5 and g.shape == (2,)
+
+
+def test_custom_loss_uses_sumstats_plus_jacobian_path():
+    class Custom(ErfBinnedModel):
+        def calc_loss_from_sumstats(self, sumstats, sumstats_aux=None,
+                                    randkey=None):
+            return torch.sum(torch.sqrt(sumstats + 1e-6))
+
+    g = torch.Generator().manual_seed(1)
+    x = (10.0 + 1.3 * torch.rand(8000, generator=g)).float()
+    m = Custom(x=x.to(dev()), bin_edges=np.linspace(9, 10, 8), volume=80.0,
+               comm=SELF, device=dev())
+    twin = Custom(x=x, bin_edges=np.linspace(9, 10, 8), volume=80.0,
+                  comm=SELF, device="cpu")
+    p = [-1.95, 0.22]
+    loss, grad = m.calc_loss_and_grad_from_params(p)
+    rl, rg = twin.calc_loss_and_grad_from_params(p)
+    assert torch.allclose(loss.cpu(), rl, rtol=1e-5)
+    assert torch.allclose(grad.cpu(), rg, rtol=2e-4, atol=1e-7)
+    traj = m.run_adam(p, nsteps=3)
+    assert traj.shape == (4, 2) and traj.is_cuda
+
+
+def test_lhs_scan_batched_matches_loop():
+    m, x, w, edges = make(n=5_000, k=10)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    params, sumstats, losses = m.run_lhs_param_scan(
+        [-2.5, 0.15], [-1.5, 0.4], 2, 20, seed=5)
+    assert sumstats.shape == (20, 10) and losses.shape == (20,)
+    for i in (0, 7, 19):
+        s = m.calc_sumstats_from_params(params[i])
+        assert np.allclose(sumstats[i], s.cpu().numpy(), rtol=1e-6)
+        assert np.isclose(losses[i], float(m.calc_loss_from_params(params[i])),
+                          rtol=1e-5)
+
+
+def test_generic_model_on_gpu_uses_device_tensors():
+    data = smf.make_smf_data(5_000, comm=SELF, device=dev())
+    model = smf.MySMFModel(aux_data=data, comm=SELF, device=dev())
+    loss, grad = model.calc_loss_and_grad_from_params([-1.9, 0.3])
+    assert loss.is_cuda and grad.is_cuda
+    native = SMFModel(aux_data=data, comm=SELF, device=dev())
+    nl, ng = native.calc_loss_and_grad_from_params([-1.9, 0.3])
+    assert torch.allclose(loss, nl, rtol=2e-4)
+    assert torch.allclose(grad, ng, rtol=2e-3, atol=1e-6)
+
+
+def test_adam_kernel_matches_formula():
+    import ctypes as C
+    from multigrad_b200.ops import _lib
+    lib = _lib.load()
+    n = 37
+    g = torch.Generator().manual_seed(2)
+    p = torch.randn(n, generator=g)
+    grad = torch.randn(n, generator=g)
+    m0, v0 = torch.rand(n, generator=g), torch.rand(n, generator=g)
+    dp, dg, dm, dv = (t.clone().to(dev()) for t in (p, grad, m0, v0))
+    rc = lib.mgb_adam_update(dp.data_ptr(), dg.data_ptr(), dm.data_ptr(),
+                             dv.data_ptr(), 4, n, 0.01, 0.9, 0.999, 1e-8,
+                             C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    _lib.check(rc)
+    rp, rm, rv = adam.adam_update(4, p, grad, m0, v0, 0.01)
+    assert torch.allclose(dp.cpu(), rp, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(dm.cpu(), rm, rtol=1e-6)
+    assert torch.allclose(dv.cpu(), rv, rtol=1e-6)
+
+
+def test_pointer_jump_kernel():
+    from multigrad_b200.experimental import diffdesi
+    rng = np.random.default_rng(0)
+    n = 5000
+    parent = np.arange(n)
+    for i in range(1, n):                 # random forest, depth up to ~log n
+        if rng.random() < 0.8:
+            parent[i] = rng.integers(0, i)
+    want = diffdesi.find_ultimate_top_indices(parent)
+    got = diffdesi.find_ultimate_top_indices(
+        torch.as_tensor(parent, device=dev()))
+    assert got.is_cuda and np.array_equal(got.cpu().numpy(), want)
+    chain = np.maximum(np.arange(200) - 1, 0)          # depth 199 > 2**50? no
+    assert np.array_equal(
+        diffdesi.find_ultimate_top_indices(
+            torch.as_tensor(chain, device=dev())).cpu().numpy(),
+        np.zeros(200, dtype=np.int64))
+    s, r = diffdesi.sort_all_by_ultimate_top_dump(
+        torch.as_tensor(parent, device=dev()),
+        [torch.arange(n, device=dev())],
+        [torch.as_tensor(parent, device=dev())])
+    s2, r2 = diffdesi.sort_all_by_ultimate_top_dump(parent, [np.arange(n)],
+                                                    [parent])
+    assert np.array_equal(r[0].cpu().numpy(), r2[0])
+
+
+def test_library_is_loaded_and_errors_are_loud():
+    import ctypes as C
+    from multigrad_b200.ops import _lib
+    lib = _lib.load()
+    assert any("libmgb200" in line for line in open("/proc/self/maps"))
+    pt = _lib.MgbPeerTable()
+    pt.world = 1
+    x = torch.zeros(8, device=dev())
+    rc = lib.mgb_allreduce_sum(C.byref(pt), x.data_ptr(), 8, 7, 0, None)
+    assert rc != 0 and b"dtype" in lib.mgb_last_error()
+    with pytest.raises(ValueError):
+        ErfBinnedModel(x=x, bin_edges=np.linspace(0, 1, 40), comm=SELF,
+                       device=dev()).plan()
