@@ -27,11 +27,6 @@
 #include <math.h>
 #include "mgb_common.cuh"
 
-#define EB_BLOCK 256
-#define EB_WARPS (EB_BLOCK / 32)
-#define EB_CTAS_PER_SM 2
-#define EB_NBMAX 16
-#define EB_PAD_EDGE 3.0e18f   // pad edge: zs^2 overflows -> g = 0, zs*g = 0
 #define EB_SENTINEL_X 1.0e30f // padding object: contributes exactly zero
 
 namespace {
@@ -72,49 +67,94 @@ __device__ __forceinline__ float2 vfma(float2 a, float2 b, float2 c) {
 #define EB_HSCALE (0.5f / EB_KAPPA)
 #define EB_ZS_SKIP 12.4f  // |zs| beyond which g and q flush to zero
 
+// Per-edge accumulators are scalar: a packed FADD2 and two FADDs cost the
+// same FMA-pipe time (the pipe retires 32 fp32 lanes per cycle either way) and
+// the issue slots are not the limiter, while four registers per edge are what
+// lets ptxas keep ET independent Horner chains in flight.
 struct EdgeAcc {
-  float2 T, O, G, Z;
+  float T, O, G, Z;
 };
 
-// Contribution of a pair of objects (scaled coordinate us, weight wt) to the
-// accumulators of one edge with scaled position cs.
-template <bool WEIGHTED>
-__device__ __forceinline__ void edge_pair(EdgeAcc& a, float cs, float2 us,
-                                          float2 wt) {
-  const float2 zs = vadd(f2s(cs), f2(-us.x, -us.y));
-  const float2 zz = vmul(zs, zs);
-  float2 g = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
-  const float2 d = vfma(f2(fabsf(zs.x), fabsf(zs.y)), f2s(EB_HSCALE),
-                        f2s(1.0f));
-  const float2 t = f2(mgb_rcp(d.x), mgb_rcp(d.y));
-  // Horner; coefficients pre-halved so that p = erfcx/2 / t
-  float2 p = f2s(0.5f * MGB_ERFCX_C8);
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C7));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C6));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C5));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C4));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C3));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C2));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C1));
-  p = vfma(p, t, f2s(0.5f * MGB_ERFCX_C0));
-  if (WEIGHTED) g = vmul(g, wt);
-  const float2 q = vmul(vmul(p, t), g);  // (w) * 1/2 erfc(|z|)
-  // ts = +q for z < 0, -q for z >= 0  (set the sign bit from ~sign(zs))
-  float2 ts;
-  ts.x = __uint_as_float(__float_as_uint(q.x) |
-                         (~__float_as_uint(zs.x) & 0x80000000u));
-  ts.y = __uint_as_float(__float_as_uint(q.y) |
-                         (~__float_as_uint(zs.y) & 0x80000000u));
-  float2 o;
-  if (WEIGHTED) {
-    o = f2(zs.x >= 0.0f ? wt.x : 0.0f, zs.y >= 0.0f ? wt.y : 0.0f);
-  } else {
-    o = f2(zs.x >= 0.0f ? 1.0f : 0.0f, zs.y >= 0.0f ? 1.0f : 0.0f);
+// Contribution of a pair of objects (centred coordinate xc, weight wt) to the
+// accumulators of the ET edges of a group, zs_e = cs_e - ks*xc.
+//
+// The ET chains are written *stage by stage* (all edges do step i before any
+// edge does step i+1): ptxas keeps that order, so every warp always has ET
+// independent FFMA2 streams in flight and the 8-deep Horner recurrence never
+// exposes its latency (the chain-by-chain form ran at 62% FMA-pipe
+// utilisation with "wait" as the top stall reason; see profiles/).
+template <int ET, bool WEIGHTED>
+__device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
+                                           const float* __restrict__ cs,
+                                           float ks, float2 xc, float2 wt) {
+  float2 zs[ET], t[ET], g[ET], p[ET];
+#pragma unroll
+  for (int e = 0; e < ET; ++e) zs[e] = vfma(xc, f2s(-ks), f2s(cs[e]));
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    const float2 d = vfma(f2(fabsf(zs[e].x), fabsf(zs[e].y)), f2s(EB_HSCALE),
+                          f2s(1.0f));
+    t[e] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
   }
-  a.T = vadd(a.T, ts);
-  a.O = vadd(a.O, o);
-  a.G = vadd(a.G, g);
-  a.Z = vfma(zs, g, a.Z);
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    const float2 zz = vmul(zs[e], zs[e]);
+    g[e] = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
+  }
+  // Horner; coefficients pre-halved so that p = erfcx/2 / t
+#pragma unroll
+  for (int e = 0; e < ET; ++e)
+    p[e] = vfma(f2s(0.5f * MGB_ERFCX_C8), t[e], f2s(0.5f * MGB_ERFCX_C7));
+#define EB_HORNER(C)                                         \
+  _Pragma("unroll") for (int e = 0; e < ET; ++e) p[e] =      \
+      vfma(p[e], t[e], f2s(0.5f * (C)));
+  EB_HORNER(MGB_ERFCX_C6)
+  EB_HORNER(MGB_ERFCX_C5)
+  EB_HORNER(MGB_ERFCX_C4)
+  EB_HORNER(MGB_ERFCX_C3)
+  EB_HORNER(MGB_ERFCX_C2)
+  EB_HORNER(MGB_ERFCX_C1)
+  EB_HORNER(MGB_ERFCX_C0)
+#undef EB_HORNER
+#pragma unroll
+  for (int e = 0; e < ET; ++e) p[e] = vmul(p[e], t[e]);
+  if (WEIGHTED) {
+#pragma unroll
+    for (int e = 0; e < ET; ++e) g[e] = vmul(g[e], wt);
+  }
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    const float2 q = vmul(p[e], g[e]);  // (w) * 1/2 erfc(|z|)
+    // ts = +q for z < 0, -q for z >= 0  (set the sign bit from ~sign(zs))
+    float2 ts;
+    ts.x = __uint_as_float(__float_as_uint(q.x) |
+                           (~__float_as_uint(zs[e].x) & 0x80000000u));
+    ts.y = __uint_as_float(__float_as_uint(q.y) |
+                           (~__float_as_uint(zs[e].y) & 0x80000000u));
+    a[e].T += ts.x;
+    a[e].T += ts.y;
+  }
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    if (WEIGHTED) {
+      a[e].O += zs[e].x >= 0.0f ? wt.x : 0.0f;
+      a[e].O += zs[e].y >= 0.0f ? wt.y : 0.0f;
+    } else {
+      // unweighted: count the objects *below* the edge on the integer pipe
+      // (sign bit of zs; the bit pattern of O is an int32 counter)
+      int c = __float_as_int(a[e].O);
+      c += (int)(__float_as_uint(zs[e].x) >> 31);
+      c += (int)(__float_as_uint(zs[e].y) >> 31);
+      a[e].O = __int_as_float(c);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    a[e].G += g[e].x;
+    a[e].G += g[e].y;
+    a[e].Z = fmaf(zs[e].x, g[e].x, a[e].Z);
+    a[e].Z = fmaf(zs[e].y, g[e].y, a[e].Z);
+  }
 }
 
 __device__ __forceinline__ float bound_inverse(int kind, float lo, float hi,
@@ -145,20 +185,163 @@ __device__ __forceinline__ float bound_jac(int kind, float lo, float hi,
   return 1.0f;
 }
 
-template <int NB, bool WEIGHTED>
-__global__ void __launch_bounds__(EB_BLOCK, EB_CTAS_PER_SM)
+// ---------------------------------------------------------------------------
+// Work decomposition.  The E = K+1 edges are split into NG groups of at most
+// EB_ET_MAX consecutive edges; a warp belongs to one group and only carries the
+// accumulators of that group's edges (8 registers per edge), which keeps the
+// kernel at <= 85 registers and 22-24 resident warps per SM.  Every group has
+// to see every object of the CTA, so a group with more edges gets
+// proportionally more warps (edge counts 6/5 -> 6 and 5 warps): all warps do
+// the same amount of work.  Per-edge sums are independent, so no edge is ever
+// evaluated twice; bin differences are taken after the CTA-level reduction.
+// ---------------------------------------------------------------------------
+#ifndef EB_ET_MAX
+#define EB_ET_MAX 4
+#endif
+#ifndef EB_MIN_CTAS
+#define EB_MIN_CTAS 2
+#endif
+#ifndef EB_TARGET_WARPS
+#define EB_TARGET_WARPS 24
+#endif
+#define EB_MAX_GROUPS ((MGB_MAX_BINS + 1 + EB_ET_MAX - 1) / EB_ET_MAX)
+#define EB_MAX_WARPS 12
+#define EB_MAX_EDGES (MGB_MAX_BINS + 1)
+
+struct EbLayout {
+  int ng;                       // number of edge groups
+  int nwarps;                   // warps per CTA
+  int e0[EB_MAX_GROUPS + 1];    // first edge of group g (e0[ng] = E)
+  int w0[EB_MAX_GROUPS + 1];    // first warp of group g (w0[ng] = nwarps)
+};
+
+// Accumulate the ET edges [e_first, e_first+ET) over the tiles of this CTA that
+// belong to warp `wj` of `wpg` warps in the group; leave the warp-reduced sums
+// (T, O, G, Z per edge) in s_out[4*ET] (lane 0 writes).
+template <int ET, bool WEIGHTED>
+__device__ __forceinline__ void accumulate_group(
+    const MgbErfBinModel& md, const float* __restrict__ cs_all, int e_first,
+    float ks, float x0, int wj, int wpg, int lane, double* s_out) {
+  float cs[ET];
+  EdgeAcc acc[ET];
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    cs[e] = cs_all[e_first + e];
+    acc[e].T = 0.f; acc[e].O = 0.f;
+    acc[e].G = 0.f; acc[e].Z = 0.f;
+  }
+  const float cs_lo = cs[0], cs_hi = cs[ET - 1];
+  const float4* __restrict__ x4 = reinterpret_cast<const float4*>(md.x);
+  const float4* __restrict__ w4 = reinterpret_cast<const float4*>(md.w);
+  const long long n4 = md.n >> 2;
+  // tile = 32 consecutive float4 (128 objects); CTA c owns tiles c, c+G, ...;
+  // within the CTA warp wj of the group takes every wpg-th of them.
+  const long long tstride = (long long)gridDim.x * wpg * 32;
+  long long i0 = ((long long)blockIdx.x + (long long)wj * gridDim.x) * 32;
+
+  auto fetch = [&](long long base, float4& xv, float4& wv) {
+    const long long i = base + lane;
+    if (i < n4) {
+      xv = __ldg(x4 + i);
+      if (WEIGHTED) wv = __ldg(w4 + i);
+    } else {
+      xv = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
+                       EB_SENTINEL_X);
+      if (WEIGHTED) wv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i == n4) {  // ragged tail: the last n % 4 objects
+        const long long b4 = n4 << 2;
+        const int rem = (int)(md.n - b4);
+        if (rem > 0) xv.x = md.x[b4];
+        if (rem > 1) xv.y = md.x[b4 + 1];
+        if (rem > 2) xv.z = md.x[b4 + 2];
+        if (WEIGHTED) {
+          if (rem > 0) wv.x = md.w[b4];
+          if (rem > 1) wv.y = md.w[b4 + 1];
+          if (rem > 2) wv.z = md.w[b4 + 2];
+        }
+      }
+    }
+  };
+
+  float4 xn, wn = make_float4(1.f, 1.f, 1.f, 1.f);
+  if (i0 < n4 + 1) fetch(i0, xn, wn);
+  // The trip count is warp-uniform (i0 does not depend on the lane) because the
+  // body votes with __all_sync.  The next tile is fetched before the current
+  // one is consumed (register double buffering hides the DRAM latency).
+  for (; i0 < n4 + 1; i0 += tstride) {
+    const float4 xv = xn, wv = wn;
+    if (i0 + tstride < n4 + 1) fetch(i0 + tstride, xn, wn);
+    const float2 xcA = vadd(f2(xv.x, xv.y), f2s(-x0));
+    const float2 xcB = vadd(f2(xv.z, xv.w), f2s(-x0));
+    // objects for which every edge of this group is saturated contribute
+    // nothing to any difference between edges: skip them warp-uniformly
+    const float cmin = fminf(fminf(xcA.x, xcA.y), fminf(xcB.x, xcB.y));
+    const float cmax = fmaxf(fmaxf(xcA.x, xcA.y), fmaxf(xcB.x, xcB.y));
+    const bool far = (fmaf(-ks, cmax, cs_lo) > EB_ZS_SKIP) ||
+                     (fmaf(-ks, cmin, cs_hi) < -EB_ZS_SKIP);
+    if (__all_sync(0xffffffffu, far)) {
+      // A skipped lane still has to keep the hard counts consistent with the
+      // other edge groups, for which the same objects may not be saturated.
+      if (WEIGHTED) {
+        // O = weight of objects at or above the edge: all four objects of a
+        // lane that is saturated on the high side (padding has weight 0)
+        if (fmaf(-ks, cmax, cs_lo) > EB_ZS_SKIP) {
+          const float cnt = (wv.x + wv.y) + (wv.z + wv.w);
+#pragma unroll
+          for (int e = 0; e < ET; ++e) acc[e].O += cnt;
+        }
+      } else {
+        // O = number of objects below the edge: all four objects of a lane
+        // saturated on the low side (padding objects sit there too, in every
+        // group alike, so they cancel in the differences between edges)
+        if (fmaf(-ks, cmin, cs_hi) < -EB_ZS_SKIP) {
+#pragma unroll
+          for (int e = 0; e < ET; ++e)
+            acc[e].O = __int_as_float(__float_as_int(acc[e].O) + 4);
+        }
+      }
+      continue;
+    }
+    edges_pair<ET, WEIGHTED>(acc, cs, ks, xcA, f2(wv.x, wv.y));
+    edges_pair<ET, WEIGHTED>(acc, cs, ks, xcB, f2(wv.z, wv.w));
+  }
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    const float t = mgb_warp_sum(acc[e].T);
+    // unweighted O counts objects with z < 0: Phi = (N - O) + T, and N drops
+    // out of every difference between edges
+    const double o =
+        WEIGHTED ? (double)mgb_warp_sum(acc[e].O)
+                 : -(double)__reduce_add_sync(0xffffffffu,
+                                              __float_as_int(acc[e].O));
+    const float g = mgb_warp_sum(acc[e].G);
+    const float z = mgb_warp_sum(acc[e].Z);
+    if (lane == 0) {
+      s_out[4 * e + 0] = (double)t;
+      s_out[4 * e + 1] = o;
+      s_out[4 * e + 2] = (double)g;
+      s_out[4 * e + 3] = (double)z;
+    }
+  }
+}
+
+template <int ET_HI, bool WEIGHTED>
+__global__ void __launch_bounds__(EB_MAX_WARPS * 32, EB_MIN_CTAS)
 erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
-                   const MgbPeerTable pt, double* __restrict__ partials,
-                   unsigned* __restrict__ counters, const int npass) {
-  constexpr int E = NB + 1;
+                   const MgbPeerTable pt, const EbLayout lay,
+                   double* __restrict__ partials,
+                   unsigned* __restrict__ counters) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nthreads = blockDim.x;
   const int b = blockIdx.y;
   const int G = gridDim.x;
   const int K = md.nbins;
-  const int KP = npass * NB;   // padded bin count
-  const int MP = 3 * KP;       // doubles per CTA partial
+  const int E = K + 1;
+  const int MP = 3 * K;  // doubles per CTA partial
 
-  __shared__ double s_warp[EB_WARPS][4 * (EB_NBMAX + 1)];
+  __shared__ float s_cs[EB_MAX_EDGES];
+  __shared__ double s_warp[EB_MAX_WARPS][4 * EB_ET_MAX];
+  __shared__ double s_edge[EB_MAX_EDGES][4];
   __shared__ double s_tot[3 * MGB_MAX_BINS];
   __shared__ double s_stage[MGB_MAX_WORLD * 3 * MGB_MAX_BINS];
   __shared__ int s_is_last;
@@ -171,114 +354,65 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
       (a.mode >= MGB_MODE_ADAM) ? a.opt_p : (a.params + (size_t)b * md.nparams);
   const float p_mu = pv[md.mu_idx];
   const float p_sg = pv[md.sig_idx];
-  const float sigma = md.sigma_link == 1 ? exp10f(p_sg) : p_sg;
-  // ks = kappa / (sqrt(2) sigma):  us = (x + p_mu) * ks,  cs_e = edge_e * ks
-  const float ks = EB_KAPPA * 0.7071067811865476f / sigma;
-  const float us0 = p_mu * ks;
+  const double sigma_d =
+      md.sigma_link == 1 ? exp10((double)p_sg) : (double)p_sg;
+  // Scaled, *centred* coordinates: with xc = x - x0 (exact in fp32 for data
+  // within a factor two of x0) and ks = kappa/(sqrt2 sigma),
+  //     zs_e = cs_e - ks*xc,   cs_e = (edge_e - p_mu - x0) * ks
+  // cs_e is formed in fp64 so that zs never subtracts two O(10) numbers.
+  const double ks_d = 1.2011224087864498 * 0.7071067811865476 / sigma_d;
+  const float ks = (float)ks_d;
+  const float x0 = md.x0;
+  if (tid < E)
+    s_cs[tid] =
+        (float)(((double)md.edges[tid] - ((double)p_mu + (double)x0)) * ks_d);
+  __syncthreads();
 
-  const float4* __restrict__ x4 = reinterpret_cast<const float4*>(md.x);
-  const float4* __restrict__ w4 = reinterpret_cast<const float4*>(md.w);
-  const long long n4 = md.n >> 2;
-  const long long gstride = (long long)G * EB_BLOCK;
+  // ---- main loop: this warp's edge group ------------------------------------
+  {
+    int g = 0;
+    while (g + 1 < lay.ng && warp >= lay.w0[g + 1]) ++g;
+    const int e_first = lay.e0[g];
+    const int et = lay.e0[g + 1] - e_first;
+    const int wpg = lay.w0[g + 1] - lay.w0[g];
+    const int wj = warp - lay.w0[g];
+    if (et == ET_HI) {
+      accumulate_group<ET_HI, WEIGHTED>(md, s_cs, e_first, ks, x0, wj, wpg,
+                                        lane, s_warp[warp]);
+    } else {
+      accumulate_group<(ET_HI > 1 ? ET_HI - 1 : 1), WEIGHTED>(
+          md, s_cs, e_first, ks, x0, wj, wpg, lane, s_warp[warp]);
+    }
+  }
+  __syncthreads();
 
-  for (int pass = 0; pass < npass; ++pass) {
-    float cs[E];
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-      const int ge = pass * NB + e;
-      cs[e] = (ge <= K ? md.edges[ge] : EB_PAD_EDGE) * ks;
+  // ---- CTA reduction in fp64: per-edge totals, then bin differences --------
+  for (int j = tid; j < 4 * E; j += nthreads) {
+    const int e = j >> 2, q = j & 3;
+    int g = 0;
+    while (g + 1 < lay.ng && e >= lay.e0[g + 1]) ++g;
+    double s = 0.0;
+    for (int w = lay.w0[g]; w < lay.w0[g + 1]; ++w)
+      s += s_warp[w][4 * (e - lay.e0[g]) + q];
+    s_edge[e][q] = s;
+  }
+  __syncthreads();
+  for (int j = tid; j < MP; j += nthreads) {
+    const int q = j / K, k = j - q * K;
+    double val;
+    if (q == 0) {
+      val = (s_edge[k + 1][1] - s_edge[k][1]) + (s_edge[k + 1][0] - s_edge[k][0]);
+    } else if (q == 1) {
+      val = s_edge[k + 1][2] - s_edge[k][2];
+    } else {
+      val = s_edge[k + 1][3] - s_edge[k][3];
     }
-    EdgeAcc acc[E];
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-      acc[e].T = f2s(0.f); acc[e].O = f2s(0.f);
-      acc[e].G = f2s(0.f); acc[e].Z = f2s(0.f);
-    }
-    const float cs_lo = cs[0];
-    const float cs_hi = (pass * NB + NB <= K) ? cs[NB] : md.edges[K] * ks;
-
-    // The trip count is warp-uniform (i0 does not depend on the lane) because
-    // the body votes with __all_sync; lanes past the end process padding
-    // objects that contribute exactly zero.
-    for (long long i0 = (long long)blockIdx.x * EB_BLOCK + warp * 32;
-         i0 < n4 + 1; i0 += gstride) {
-      const long long i = i0 + lane;
-      float4 xv, wv = make_float4(1.f, 1.f, 1.f, 1.f);
-      if (i < n4) {
-        xv = __ldg(x4 + i);
-        if (WEIGHTED) wv = __ldg(w4 + i);
-      } else {
-        xv = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
-                         EB_SENTINEL_X);
-        if (WEIGHTED) wv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i == n4) {  // ragged tail: the last n % 4 objects
-          const long long base = n4 << 2;
-          const int rem = (int)(md.n - base);
-          if (rem > 0) xv.x = md.x[base];
-          if (rem > 1) xv.y = md.x[base + 1];
-          if (rem > 2) xv.z = md.x[base + 2];
-          if (WEIGHTED) {
-            if (rem > 0) wv.x = md.w[base];
-            if (rem > 1) wv.y = md.w[base + 1];
-            if (rem > 2) wv.z = md.w[base + 2];
-          }
-        }
-      }
-      const float2 usA = vfma(f2(xv.x, xv.y), f2s(ks), f2s(us0));
-      const float2 usB = vfma(f2(xv.z, xv.w), f2s(ks), f2s(us0));
-      // objects whose every edge is saturated contribute nothing to any
-      // *difference* between edges: skip them warp-uniformly
-      const float umin = fminf(fminf(usA.x, usA.y), fminf(usB.x, usB.y));
-      const float umax = fmaxf(fmaxf(usA.x, usA.y), fmaxf(usB.x, usB.y));
-      const bool far = (cs_lo - umax > EB_ZS_SKIP) || (cs_hi - umin < -EB_ZS_SKIP);
-      if (__all_sync(0xffffffffu, far)) continue;
-#pragma unroll
-      for (int e = 0; e < E; ++e) {
-        edge_pair<WEIGHTED>(acc[e], cs[e], usA, f2(wv.x, wv.y));
-        edge_pair<WEIGHTED>(acc[e], cs[e], usB, f2(wv.z, wv.w));
-      }
-    }
-
-    // ---- CTA reduction: fp32 inside the warp, fp64 across warps -----------
-#pragma unroll
-    for (int e = 0; e < E; ++e) {
-      float t = mgb_warp_sum(acc[e].T.x + acc[e].T.y);
-      float o = mgb_warp_sum(acc[e].O.x + acc[e].O.y);
-      float g = mgb_warp_sum(acc[e].G.x + acc[e].G.y);
-      float z = mgb_warp_sum(acc[e].Z.x + acc[e].Z.y);
-      if (lane == 0) {
-        s_warp[warp][4 * e + 0] = (double)t;
-        s_warp[warp][4 * e + 1] = (double)o;
-        s_warp[warp][4 * e + 2] = (double)g;
-        s_warp[warp][4 * e + 3] = (double)z;
-      }
-    }
-    __syncthreads();
-    if (tid < 4 * E) {
-      double s = 0.0;
-#pragma unroll
-      for (int w = 0; w < EB_WARPS; ++w) s += s_warp[w][tid];
-      s_warp[0][tid] = s;  // only thread `tid` touches column `tid` here
-    }
-    __syncthreads();
-    if (tid < 3 * NB) {
-      const int q = tid / NB, k = tid - q * NB;
-      double val;
-      if (q == 0) {
-        val = (s_warp[0][4 * (k + 1) + 1] - s_warp[0][4 * k + 1]) +
-              (s_warp[0][4 * (k + 1) + 0] - s_warp[0][4 * k + 0]);
-      } else if (q == 1) {
-        val = s_warp[0][4 * (k + 1) + 2] - s_warp[0][4 * k + 2];
-      } else {
-        val = s_warp[0][4 * (k + 1) + 3] - s_warp[0][4 * k + 3];
-      }
-      partials[((size_t)b * G + blockIdx.x) * MP + q * KP + pass * NB + k] = val;
-    }
-    __syncthreads();
+    partials[((size_t)b * G + blockIdx.x) * MP + j] = val;
   }
 
   // ---- last-CTA election ---------------------------------------------------
   __threadfence();
+  __syncthreads();
   if (tid == 0) {
     const unsigned ticket = atomicAdd(&counters[b], 1u);
     s_is_last = (ticket == (unsigned)(G - 1));
@@ -290,7 +424,8 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   // ---- fixed-order grid reduction: 8 lanes per value -----------------------
   {
     const int sub = tid & 7, grp = tid >> 3;
-    for (int j0 = 0; j0 < MP; j0 += EB_BLOCK / 8) {
+    const int ngrp = nthreads >> 3;
+    for (int j0 = 0; j0 < MP; j0 += ngrp) {
       const int j = j0 + grp;
       double accd = 0.0;
       if (j < MP) {
@@ -300,11 +435,7 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
       accd += __shfl_xor_sync(0xffffffffu, accd, 4);
       accd += __shfl_xor_sync(0xffffffffu, accd, 2);
       accd += __shfl_xor_sync(0xffffffffu, accd, 1);
-      if (j < MP && sub == 0) {
-        // compact away the padded bins: value (q, k) -> q*K + k
-        const int q = j / KP, k = j - q * KP;
-        if (k < K) s_tot[q * K + k] = accd;
-      }
+      if (j < MP && sub == 0) s_tot[j] = accd;
     }
   }
   if (tid == 0) counters[b] = 0u;  // ready for the next launch
@@ -315,7 +446,7 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
 
   // ---- epilogue (warp 0; lane k owns bin k) --------------------------------
   if (warp != 0) return;
-  const double sig = (double)sigma;
+  const double sig = sigma_d;
   const double inv = 0.7071067811865476 / sig;             // 1/(sqrt2 sigma)
   const double rsqrtpi = 0.5641895835477563;               // 1/sqrt(pi)
   const double dsdp = md.sigma_link == 1 ? 2.302585092994046 * sig : 1.0;
@@ -415,51 +546,88 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
 }
 
 typedef void (*eb_kernel_t)(const MgbErfBinModel, const MgbStepArgs,
-                            const MgbPeerTable, double*, unsigned*, const int);
+                            const MgbPeerTable, const EbLayout, double*,
+                            unsigned*);
 
 template <bool W>
-eb_kernel_t pick_kernel(int nb) {
-  switch (nb) {
-#define EB_CASE(N) \
-  case N:          \
-    return erfbin_step_kernel<N, W>;
-    EB_CASE(1) EB_CASE(2) EB_CASE(3) EB_CASE(4) EB_CASE(5) EB_CASE(6)
-    EB_CASE(7) EB_CASE(8) EB_CASE(9) EB_CASE(10) EB_CASE(11) EB_CASE(12)
-    EB_CASE(13) EB_CASE(14) EB_CASE(15) EB_CASE(16)
-#undef EB_CASE
+eb_kernel_t pick_kernel(int et_hi) {
+  switch (et_hi) {
+    case 1: return erfbin_step_kernel<1, W>;
+    case 2: return erfbin_step_kernel<2, W>;
+    case 3: return erfbin_step_kernel<3, W>;
+    case 4: return erfbin_step_kernel<4, W>;
+#if EB_ET_MAX >= 5
+    case 5: return erfbin_step_kernel<5, W>;
+#endif
+#if EB_ET_MAX >= 6
+    case 6: return erfbin_step_kernel<6, W>;
+#endif
   }
   return nullptr;
 }
 
-int g_grid_cache[64] = {0};
+// Edge groups and warps per group for K bins (see the comment above EbLayout).
+EbLayout make_layout(int nbins, int* et_hi_out) {
+  EbLayout L;
+  const int E = nbins + 1;
+  L.ng = (E + EB_ET_MAX - 1) / EB_ET_MAX;
+  const int lo = E / L.ng, extra = E % L.ng;  // `extra` groups get lo+1 edges
+  const int et_hi = lo + (extra ? 1 : 0);
+  // Warps per group: proportional to the group's edge count while one warp
+  // per edge fits in a CTA (perfect balance), else the same number of warps
+  // for every group (a 3-edge group then idles 25% of the time).
+  const int even = EB_MAX_WARPS / L.ng > 0 ? EB_MAX_WARPS / L.ng : 1;
+  int e = 0, w = 0;
+  for (int g = 0; g < L.ng; ++g) {
+    const int et = lo + (g < extra ? 1 : 0);
+    L.e0[g] = e;
+    L.w0[g] = w;
+    e += et;
+    w += (E <= EB_MAX_WARPS) ? et : even;
+  }
+  L.e0[L.ng] = e;
+  L.w0[L.ng] = w;
+  L.nwarps = w;
+  *et_hi_out = et_hi;
+  return L;
+}
 
-}  // namespace
+int g_sm_cache[64] = {0};
 
-extern "C" int mgb_erfbin_grid(void) {
+int sm_count() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-  if (dev >= 0 && dev < 64 && g_grid_cache[dev]) return g_grid_cache[dev];
+  if (dev >= 0 && dev < 64 && g_sm_cache[dev]) return g_sm_cache[dev];
   int sms = 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) !=
       cudaSuccess)
     return 0;
-  const int g = sms * EB_CTAS_PER_SM;
-  if (dev >= 0 && dev < 64) g_grid_cache[dev] = g;
-  return g;
+  if (dev >= 0 && dev < 64) g_sm_cache[dev] = sms;
+  return sms;
 }
 
-static inline void eb_layout(int nbins, int* npass, int* nb) {
-  *npass = (nbins + EB_NBMAX - 1) / EB_NBMAX;
-  *nb = (nbins + *npass - 1) / *npass;
+// CTAs per SM so that about 24 warps are resident
+int grid_for(int nbins) {
+  int et_hi;
+  const EbLayout L = make_layout(nbins, &et_hi);
+  int per_sm = EB_TARGET_WARPS / L.nwarps;
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  return sm_count() * per_sm;
+}
+
+}  // namespace
+
+extern "C" int mgb_erfbin_grid(int nbins) {
+  if (nbins < 1 || nbins > MGB_MAX_BINS) return 0;
+  return grid_for(nbins);
 }
 
 extern "C" uint64_t mgb_erfbin_scratch_bytes(int nbins, int batch) {
-  int npass, nb;
   if (nbins < 1 || nbins > MGB_MAX_BINS || batch < 1) return 0;
-  eb_layout(nbins, &npass, &nb);
-  const int grid = mgb_erfbin_grid();
+  const int grid = grid_for(nbins);
   const uint64_t counters = ((uint64_t)batch * 4ull + 255ull) & ~255ull;
-  return counters + (uint64_t)batch * grid * 3ull * npass * nb * 8ull;
+  return counters + (uint64_t)batch * grid * 3ull * nbins * 8ull;
 }
 
 extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
@@ -514,9 +682,9 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
     MGB_REQUIRE(ptv.world <= MGB_MAX_WORLD && 6u * md.nbins <= ptv.ll_units,
                 MGB_ETOOBIG, "mgb_erfbin_step: peer table too small");
   }
-  int npass, nb;
-  eb_layout(md.nbins, &npass, &nb);
-  const int grid = mgb_erfbin_grid();
+  int et_hi = 0;
+  const EbLayout lay = make_layout(md.nbins, &et_hi);
+  const int grid = grid_for(md.nbins);
   MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_erfbin_step: no CUDA device");
   const uint64_t need = mgb_erfbin_scratch_bytes(md.nbins, a.batch);
   MGB_REQUIRE(scratch_bytes >= need, MGB_ETOOBIG,
@@ -526,12 +694,11 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   unsigned* counters = reinterpret_cast<unsigned*>(scratch);
   double* partials =
       reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + coff);
-  eb_kernel_t k = md.w ? pick_kernel<true>(nb) : pick_kernel<false>(nb);
-  MGB_REQUIRE(k != nullptr, MGB_ESTATE, "mgb_erfbin_step: no kernel for nb=%d",
-              nb);
-  dim3 g((unsigned)grid, (unsigned)a.batch, 1), blk(EB_BLOCK, 1, 1);
-  k<<<g, blk, 0, (cudaStream_t)stream>>>(md, a, ptv, partials, counters,
-                                         npass);
+  eb_kernel_t k = md.w ? pick_kernel<true>(et_hi) : pick_kernel<false>(et_hi);
+  MGB_REQUIRE(k != nullptr, MGB_ESTATE,
+              "mgb_erfbin_step: no kernel for %d edges per group", et_hi);
+  dim3 g((unsigned)grid, (unsigned)a.batch, 1), blk(lay.nwarps * 32, 1, 1);
+  k<<<g, blk, 0, (cudaStream_t)stream>>>(md, a, ptv, lay, partials, counters);
   MGB_CUDA_CHECK(cudaGetLastError());
   return MGB_OK;
 }

@@ -100,6 +100,9 @@ typedef struct MgbErfBinModel {
   int32_t loss_kind;     /* 0: mean (log10(s+eps)-log10(t+eps))^2
                             1: mean (s-t)^2   2: sum ((s-t)*inv_err)^2       */
   float loss_eps;
+  float x0;              /* centring constant: the kernel works on x - x0;
+                            pick a value near the bulk of the data (any value
+                            is valid, 0 disables centring)                  */
   float edges[MGB_MAX_BINS + 1];
   float norm[MGB_MAX_BINS];    /* s_k = norm_k * sum_h (Phi_{k+1}-Phi_k)     */
   float target[MGB_MAX_BINS];
@@ -145,7 +148,7 @@ typedef struct MgbStepArgs {
 
 /* scratch needed by mgb_erfbin_step: bytes for `scratch` given the batch */
 uint64_t mgb_erfbin_scratch_bytes(int nbins, int batch);
-int mgb_erfbin_grid(void);
+int mgb_erfbin_grid(int nbins);
 /* `scratch` must be zero-filled once before its first use. */
 int mgb_erfbin_step(const MgbErfBinModel* model, const MgbStepArgs* args,
                     const MgbPeerTable* pt, void* scratch,

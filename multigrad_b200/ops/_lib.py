@@ -58,7 +58,7 @@ class MgbErfBinModel(C.Structure):
         ("nbins", C.c_int32), ("nparams", C.c_int32),
         ("mu_idx", C.c_int32), ("sig_idx", C.c_int32),
         ("sigma_link", C.c_int32), ("loss_kind", C.c_int32),
-        ("loss_eps", C.c_float),
+        ("loss_eps", C.c_float), ("x0", C.c_float),
         ("edges", C.c_float * (MGB_MAX_BINS + 1)),
         ("norm", C.c_float * MGB_MAX_BINS),
         ("target", C.c_float * MGB_MAX_BINS),
@@ -187,6 +187,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.mgb_erfbin_scratch_bytes.restype = u64
     lib.mgb_erfbin_scratch_bytes.argtypes = [C.c_int, C.c_int]
     lib.mgb_erfbin_grid.restype = C.c_int
+    lib.mgb_erfbin_grid.argtypes = [C.c_int]
     lib.mgb_erfbin_step.argtypes = [C.POINTER(MgbErfBinModel),
                                     C.POINTER(MgbStepArgs),
                                     C.POINTER(MgbPeerTable), vp, u64, vp]
@@ -211,7 +212,8 @@ def load(build_if_missing: bool = True) -> C.CDLL:
         raise RuntimeError(
             f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ "
             "as g; g.build()'` (needs nvcc) before using the CUDA path")
-    lib = C.CDLL(str(LIB_PATH))
+    override = os.environ.get("MULTIGRAD_B200_LIB")   # tuning experiments
+    lib = C.CDLL(override if override else str(LIB_PATH))
     _declare(lib)
     _LIB = lib
     return lib

@@ -82,6 +82,10 @@ class ErfBinPlan:
         md.sigma_link = SIGMA_LINKS[sigma_link]
         md.loss_kind = LOSS_KINDS[loss]
         md.loss_eps = float(loss_eps)
+        # centring constant (see csrc/erfbin.cu): mean of the shard rounded to
+        # a multiple of 1/64 so that x - x0 is exact in fp32
+        x0 = float(x.double().mean().item()) if x.numel() else 0.0
+        md.x0 = round(x0 * 64.0) / 64.0 if np.isfinite(x0) else 0.0
         norm = np.broadcast_to(np.asarray(norm, dtype=np.float64), (K,))
         tgt = (np.ones(K) if target is None
                else np.asarray(target, dtype=np.float64).ravel())
