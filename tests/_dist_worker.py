@@ -232,6 +232,68 @@ def experimental_scan_gd():
     assert len(df) == 50 and abs(df["params"].iloc[-1][0] - 2.0) < 0.05
 
 
+@case
+def gpu_allreduce_kernels():
+    """K5: LL and two-shot all-reduce vs an exact host sum; every rank must
+    hold bit-identical results."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.ops import allreduce as ar
+    g = torch.Generator().manual_seed(1234)
+    for n, dtype, algo in [(1, torch.float32, 1), (3, torch.float32, 0),
+                           (30, torch.float64, 1), (1000, torch.float32, 1),
+                           (4096, torch.float32, 2), (5003, torch.float32, 0),
+                           (100_001, torch.float32, 2),
+                           ((1 << 20) + 3, torch.float32, 0),
+                           (6000, torch.float64, 0)]:
+        full = torch.randn(SIZE, n, generator=g, dtype=torch.float64)
+        mine = full[RANK].to(dtype).to(DEV)
+        want = full.to(dtype).double().sum(0)
+        for rep in range(3):            # repeated calls reuse the LL slots
+            out = ar.all_reduce_sum(mine, COMM, algo=algo)
+            torch.cuda.synchronize()
+            tol = 1e-6 if dtype == torch.float32 else 1e-13
+            err = (out.double().cpu() - want).abs().max() / want.abs().max()
+            assert err < tol * SIZE, (n, dtype, algo, rep, float(err))
+            blobs = COMM.allgather(out.cpu().numpy().tobytes())
+            assert all(b == blobs[0] for b in blobs), (n, dtype, algo)
+        assert torch.equal(mine.cpu(), full[RANK].to(dtype))   # input intact
+    # integer tensors go through float64
+    t = mg.reduce_sum(torch.arange(5, device=DEV) * (RANK + 1))
+    assert t.dtype == torch.int64
+    assert torch.equal(t.cpu(), torch.arange(5) * sum(range(1, SIZE + 1)))
+    b = torch.full((7,), float(RANK), device=DEV)
+    ar.bcast_(b, COMM, root=SIZE - 1)
+    assert torch.all(b == SIZE - 1)
+    COMM.workspace().check_error()
+
+
+@case
+def gpu_fused_step_uses_one_launch():
+    """The multi-GPU Adam step is ONE kernel launch per rank (no separate
+    collective launch) and needs no NCCL call."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.ops import erfbin, allreduce as ar
+    data = _data(40_000)
+    model = SMFModel(aux_data=data)
+    model.run_adam([-1.9, 0.3], nsteps=2)       # builds plan + workspace
+    e0, a0 = erfbin.launch_count(), ar.launch_count()
+    ep0 = COMM.workspace().epoch
+    traj, losses = model.run_adam([-1.9, 0.3], nsteps=20, learning_rate=0.01,
+                                  return_loss=True)
+    torch.cuda.synchronize()
+    assert erfbin.launch_count() - e0 == 20 and ar.launch_count() == a0
+    if SIZE > 1:
+        assert COMM.workspace().epoch - ep0 == 20   # one exchange per step
+    assert bool(torch.isfinite(traj).all()) and losses[-1] < losses[0]
+    tg = model.run_adam([-1.9, 0.3], nsteps=120, learning_rate=0.01,
+                        use_graph=True)
+    ts = model.run_adam([-1.9, 0.3], nsteps=120, learning_rate=0.01,
+                        use_graph=False)
+    assert torch.equal(tg, ts)
+
+
 def main():
     only = sys.argv[1:] or list(CASES)
     results = {}
