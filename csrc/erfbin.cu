@@ -25,6 +25,8 @@
 // (multigrad/adam.py:52-68), transforms (adam.py:192-239), simple_grad_descent
 // (multigrad/util.py:100-114).
 #include <math.h>
+#include <string.h>
+#include <mutex>
 #include "mgb_common.cuh"
 
 #define EB_SENTINEL_X 1.0e30f // padding object: contributes exactly zero
@@ -701,4 +703,94 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   k<<<g, blk, 0, (cudaStream_t)stream>>>(md, a, ptv, lay, partials, counters);
   MGB_CUDA_CHECK(cudaGetLastError());
   return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------
+// mgb_erfbin_step_static -- the same fused step for callers that have no way
+// to obtain scratch memory.
+//
+// mgb_erfbin_step needs a scratch block (the per-CTA partial sums of the grid
+// reduction plus the ticket counters) that the caller allocates.  Some callers
+// cannot do that: a plug-in that lives inside another runtime and is only
+// handed its input and output buffers (custom-call style embedding), a process
+// whose whole device memory already belongs to somebody else's pool, or code
+// running in a phase where calling the CUDA allocator is forbidden or would
+// stall the device (cudaMalloc synchronises).  For them the scratch lives in
+// the library image itself: a file-scope __device__ array of
+// MGB_STATIC_SCRATCH_BYTES (1 MiB) that every GPU which loads the library
+// keeps resident until the process exits.  This entry point calls no
+// cudaMalloc / cudaFree and no allocating library routine.
+//
+// Consequences the caller has to know about:
+//  * Size limit.  The request is refused with MGB_ETOOBIG when
+//    mgb_erfbin_scratch_bytes(nbins, batch) exceeds MGB_STATIC_SCRATCH_BYTES
+//    (batch = 1 always fits; large batched scans do not).
+//  * One array per GPU, shared by every call.  It still holds whatever the
+//    previous call left there; the ticket counters, the only part that must
+//    start at zero, are cleared on the caller's stream before each launch.
+//    Two calls that overlap on the same GPU (different streams, or different
+//    host threads) use the same partial-sum slots and race: serialise them.
+//  * Set-up.  The address of the array is looked up once per device, with
+//    that device current, by the first call made on it
+//    (cudaGetSymbolAddress: inside host code the array's name is only a
+//    host-side handle, not something a kernel can dereference).  Make that
+//    first call before any stream capture is started.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char
+    g_eb_static_scratch[MGB_STATIC_SCRATCH_BYTES];
+
+namespace {
+void* g_static_scratch_ptr[64] = {nullptr};
+std::mutex g_static_scratch_mutex;
+
+// Device address of g_eb_static_scratch on the current device (resolved once
+// per device).
+int static_scratch_address(void** out) {
+  int dev = -1;
+  MGB_CUDA_CHECK(cudaGetDevice(&dev));
+  MGB_REQUIRE(dev >= 0 && dev < 64, MGB_ESTATE,
+              "mgb_erfbin_step_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    MGB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_eb_static_scratch));
+    MGB_REQUIRE(p != nullptr, MGB_ESTATE,
+                "mgb_erfbin_step_static: cudaGetSymbolAddress returned null");
+    g_static_scratch_ptr[dev] = p;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return MGB_OK;
+}
+}  // namespace
+
+extern "C" int mgb_erfbin_step_static(const MgbErfBinModel* model,
+                                      const MgbStepArgs* args,
+                                      const MgbPeerTable* pt, void* stream) {
+  MGB_REQUIRE(model && args, MGB_EINVAL,
+              "mgb_erfbin_step_static: null argument");
+  MGB_REQUIRE(model->nbins >= 1 && model->nbins <= MGB_MAX_BINS, MGB_ETOOBIG,
+              "mgb_erfbin_step_static: nbins=%d outside [1,%d]", model->nbins,
+              MGB_MAX_BINS);
+  MGB_REQUIRE(args->batch >= 1 && args->batch <= MGB_MAX_BATCH, MGB_ETOOBIG,
+              "mgb_erfbin_step_static: batch=%d outside [1,%d]", args->batch,
+              MGB_MAX_BATCH);
+  const uint64_t need = mgb_erfbin_scratch_bytes(model->nbins, args->batch);
+  MGB_REQUIRE(need > 0, MGB_ESTATE,
+              "mgb_erfbin_step_static: no CUDA device");
+  MGB_REQUIRE(need <= (uint64_t)MGB_STATIC_SCRATCH_BYTES, MGB_ETOOBIG,
+              "mgb_erfbin_step_static: nbins=%d, batch=%d needs %llu bytes of "
+              "scratch but the built-in array holds %llu; use "
+              "mgb_erfbin_step with caller-provided scratch or a smaller batch",
+              model->nbins, args->batch, (unsigned long long)need,
+              (unsigned long long)MGB_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  const int rc = static_scratch_address(&scratch);
+  if (rc != MGB_OK) return rc;
+  // the ticket counters must start at zero; the partial sums are overwritten
+  const uint64_t counter_bytes =
+      ((uint64_t)args->batch * 4ull + 255ull) & ~255ull;
+  MGB_CUDA_CHECK(
+      cudaMemsetAsync(scratch, 0, counter_bytes, (cudaStream_t)stream));
+  return mgb_erfbin_step(model, args, pt, scratch, MGB_STATIC_SCRATCH_BYTES,
+                         stream);
 }

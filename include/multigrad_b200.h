@@ -154,6 +154,22 @@ int mgb_erfbin_step(const MgbErfBinModel* model, const MgbStepArgs* args,
                     const MgbPeerTable* pt, void* scratch,
                     uint64_t scratch_bytes, void* stream);
 
+/* Same fused step, for callers that cannot allocate scratch (a plug-in that
+ * only receives its input/output buffers from a host runtime, a process whose
+ * device memory is owned by another pool, a phase in which calling the CUDA
+ * allocator is off limits).  No counterpart in the reference: the reference
+ * has no native code and never manages device memory itself.
+ * The scratch is a built-in __device__ array of MGB_STATIC_SCRATCH_BYTES that
+ * every GPU loading the library keeps until exit; requests that need more
+ * (see mgb_erfbin_scratch_bytes) are refused with MGB_ETOOBIG.  The array is
+ * shared by all calls on a GPU: calls that overlap there race.  The first
+ * call on a device resolves the array's device address; make it before any
+ * stream capture.  Calls no cudaMalloc/cudaFree. */
+#define MGB_STATIC_SCRATCH_BYTES (1u << 20)
+int mgb_erfbin_step_static(const MgbErfBinModel* model,
+                           const MgbStepArgs* args, const MgbPeerTable* pt,
+                           void* stream);
+
 /* ------------------------------------------------------------------------
  * K3 stand-alone: Adam / bound transforms on device vectors for the generic
  * (user-defined torch model) path.  Replaces jax_opt.adam's opt_update and
