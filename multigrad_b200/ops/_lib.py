@@ -195,6 +195,10 @@ def _declare(lib: C.CDLL) -> None:
                                            C.POINTER(MgbStepArgs),
                                            C.POINTER(MgbPeerTable), vp]
     lib.mgb_erfbin_step_static.restype = C.c_int
+    if hasattr(lib, "mgb_linlink_selftest"):
+        lib.mgb_linlink_selftest.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int,
+                                             vp]
+        lib.mgb_linlink_selftest.restype = C.c_int
     lib.mgb_adam_update.argtypes = [vp, vp, vp, vp, i32, i32, f32, f32, f32,
                                     f32, vp]
     lib.mgb_pointer_jump.argtypes = [vp, vp, i64, i32, C.POINTER(i32), vp, vp]
