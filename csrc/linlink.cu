@@ -208,7 +208,559 @@ linlink_selftest_kernel(const __grid_constant__ CUtensorMap wmap,
   if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+
+// ===========================================================================
+// The fused step.
+//   warp 0        TMA producer (W tiles, 128 objects x P features, SW128)
+//   warp 1        UMMA issuer (both products) + TMEM owner
+//   warps 2..13   compute: 3 edge groups x 4 TMEM lane quadrants; thread =
+//                 one object of the tile and the <= 4 edges of its group
+// Pipeline per tile (stage s of LL_STAGES):
+//   TMA -> full_w[s] -> UMMA#1 -> mu_full[s] -> compute (tcgen05.ld mu, erfc,
+//   g -> bf16 hi/lo into G[s]) -> g_full[s] -> UMMA#2 (accumulates D2) ->
+//   empty[s] -> TMA ...
+// ===========================================================================
+constexpr int LL_STAGES = 3;
+constexpr int LL_THREADS = 448;
+constexpr int LL_CWARPS = 12;
+constexpr int LL_ET = 4;            // edges per compute group (3 groups)
+constexpr int LL_MAXE = MGB_LIN_MAX_BINS + 1;
+constexpr float LL_KAPPA = 1.2011224087864498f;
+constexpr float LL_HSCALE = 0.5f / LL_KAPPA;
+
+struct LinSmemLayout {
+  int w_bytes, th_off, g_off, total;
+};
+__host__ __device__ inline LinSmemLayout lin_smem_layout(int P) {
+  LinSmemLayout L;
+  L.w_bytes = (P / LL_FB) * LL_TILE * 128;          // per stage
+  L.th_off = LL_STAGES * L.w_bytes;
+  L.g_off = L.th_off + (P / LL_FB) * 2048;
+  L.total = L.g_off + LL_STAGES * 8192 + 16384;     // + UMMA over-read slack
+  return L;
+}
+
+__device__ __forceinline__ float ll_bound_inverse(int kind, float lo, float hi,
+                                                  float u) {
+  if (kind == 1) {
+    const float mid = 0.5f * (hi + lo), sc = (hi - lo) * 0.3183098861837907f;
+    return mid + sc * atanf(u / sc);
+  } else if (kind == 2) {
+    return 0.5f * (2.0f * lo + u + sqrtf(u * u + 4.0f));
+  } else if (kind == 3) {
+    return 0.5f * (2.0f * hi + u - sqrtf(u * u + 4.0f));
+  }
+  return u;
+}
+__device__ __forceinline__ float ll_bound_jac(int kind, float lo, float hi,
+                                              float x) {
+  if (kind == 1) {
+    const float sc = (hi - lo) * 0.3183098861837907f, r = x / sc;
+    return 1.0f / (1.0f + r * r);
+  } else if (kind == 2) {
+    return 0.5f * (1.0f + x / sqrtf(x * x + 4.0f));
+  } else if (kind == 3) {
+    return 0.5f * (1.0f - x / sqrtf(x * x + 4.0f));
+  }
+  return 1.0f;
+}
+
+template <int P>
+__global__ void __launch_bounds__(LL_THREADS, 1)
+linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
+                    const MgbLinModel md, const MgbLinArgs a,
+                    const MgbPeerTable pt, double* __restrict__ partials,
+                    unsigned* __restrict__ counter) {
+  constexpr int NFB = P / LL_FB;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const LinSmemLayout L = lin_smem_layout(P);
+  uint8_t* s_w = smem;
+  uint8_t* s_th = smem + L.th_off;
+  uint8_t* s_g = smem + L.g_off;
+
+  __shared__ uint64_t full_w[LL_STAGES], mu_full[LL_STAGES],
+      g_full[LL_STAGES], empty[LL_STAGES], d2_done;
+  __shared__ uint32_t s_tmem;
+  __shared__ float s_cs[LL_MAXE];
+  __shared__ double s_warp[LL_CWARPS][3 * LL_ET];
+  __shared__ double s_edge[LL_MAXE][3];
+  __shared__ int s_is_last, s_fail;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int G = gridDim.x;
+  const int K = md.nbins, E = K + 1;
+  const int NP = md.nfeat + 1;
+  const int M = 2 * K + K * P;     // doubles per CTA partial
+  const long long ntiles = (md.n + LL_TILE - 1) / LL_TILE;
+  const long long my_tiles =
+      ntiles > blockIdx.x ? (ntiles - blockIdx.x + G - 1) / G : 0;
+
+  const float* pv = (a.mode >= MGB_MODE_ADAM) ? a.opt_p : a.params;
+  const float p_sg = pv[md.nfeat];
+  const double sigma_d =
+      md.sigma_link == 1 ? exp10((double)p_sg) : (double)p_sg;
+  const double ks_d = 1.2011224087864498 * 0.7071067811865476 / sigma_d;
+  const float ks = (float)ks_d;
+  const float x0 = md.x0;
+
+  if (tid == 0) {
+    for (int s = 0; s < LL_STAGES; ++s) {
+      mbar_init(&full_w[s], 1);
+      mbar_init(&mu_full[s], 1);
+      mbar_init(&g_full[s], LL_CWARPS);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(&d2_done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&wmap);
+    s_fail = 0;
+  }
+  if (warp == 1) {
+    tmem_alloc(&s_tmem, 256);
+    tmem_relinquish();
+  }
+  if (tid < E)
+    s_cs[tid] = (float)(((double)md.edges[tid] - (double)x0) * ks_d);
+  write_theta_tile(s_th, pv, P, tid, LL_THREADS);   // theta planes (B of #1)
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const uint32_t tm_d2 = tmem + 64;     // P columns; D1 stages at 0,16,32
+
+  int fail = 0;
+  if (warp == 0) {
+    // ------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      for (long long it = 0; it < my_tiles; ++it) {
+        const int s = (int)(it % LL_STAGES);
+        const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
+        if (!mbar_wait(&empty[s], ph ^ 1u)) { fail = 1; break; }
+        const long long tile = blockIdx.x + it * G;
+        mbar_arrive_expect_tx(&full_w[s], (uint32_t)L.w_bytes);
+        for (int fb = 0; fb < NFB; ++fb)
+          tma_load_2d(s_w + s * L.w_bytes + fb * LL_TILE * 128, &wmap,
+                      &full_w[s], fb * LL_FB, (int)(tile * LL_TILE));
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------ UMMA issuer
+    if (lane == 0) {
+      const uint32_t id1 = idesc_bf16_f32(128, 16, false, false);
+      const uint32_t id2 = idesc_bf16_f32(128, P, false, true);
+      auto issue_jac = [&](long long jt) {
+        const int s = (int)(jt % LL_STAGES);
+        const uint32_t ph = (uint32_t)((jt / LL_STAGES) & 1);
+        if (!mbar_wait(&g_full[s], ph)) { fail = 1; return; }
+        tc_fence_after();
+        const uint32_t wb = smem_u32(s_w + s * L.w_bytes);
+        const uint32_t gb = smem_u32(s_g + s * 8192);
+        for (int kstep = 0; kstep < LL_TILE / 16; ++kstep) {
+          const uint64_t da = smem_desc_sw128(
+              gb + (kstep >> 2) * 4096 + (kstep & 3) * 32, 16, 1024);
+          const uint64_t db =
+              smem_desc_sw128(wb + kstep * 2048, LL_TILE * 128, 1024);
+          umma_bf16(tm_d2, da, db, id2, jt > 0 || kstep > 0);
+        }
+        umma_commit(&empty[s]);
+      };
+      for (long long it = 0; it < my_tiles && !fail; ++it) {
+        const int s = (int)(it % LL_STAGES);
+        const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
+        if (!mbar_wait(&full_w[s], ph)) { fail = 1; break; }
+        tc_fence_after();
+        const uint32_t wb = smem_u32(s_w + s * L.w_bytes);
+        for (int kstep = 0; kstep < P / 16; ++kstep) {
+          const int fb = kstep >> 2, kk = kstep & 3;
+          const uint64_t da =
+              smem_desc_sw128(wb + fb * LL_TILE * 128 + kk * 32, 16, 1024);
+          const uint64_t db =
+              smem_desc_sw128(smem_u32(s_th + fb * 2048) + kk * 32, 16, 1024);
+          umma_bf16(tmem + s * 16, da, db, id1, kstep > 0);
+        }
+        umma_commit(&mu_full[s]);
+        if (it > 0) issue_jac(it - 1);
+      }
+      if (my_tiles > 0 && !fail) issue_jac(my_tiles - 1);
+      umma_commit(&d2_done);
+    }
+  } else {
+    // ------------------------------------------------------ compute warps
+    const int cw = warp - 2;
+    const int grp = cw >> 2;             // edge group
+    const int quad = warp & 3;           // TMEM lane quadrant this warp owns
+    const int o = quad * 32 + lane;      // object within the tile
+    const int e_first = grp * LL_ET;
+    float cs[LL_ET];
+    float accT[LL_ET], accZ[LL_ET];
+    int accO[LL_ET];
+#pragma unroll
+    for (int e = 0; e < LL_ET; ++e) {
+      cs[e] = (e_first + e < E) ? s_cs[e_first + e] : 3.0e18f;
+      accT[e] = 0.f; accZ[e] = 0.f; accO[e] = 0;
+    }
+    long long obj = (long long)blockIdx.x * LL_TILE + o;
+    float xn = (my_tiles > 0 && obj < md.n) ? __ldg(md.x + obj) : 1.0e30f;
+    for (long long it = 0; it < my_tiles; ++it) {
+      const int s = (int)(it % LL_STAGES);
+      const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
+      const float xv = xn;
+      const bool valid = obj < md.n;
+      obj += (long long)G * LL_TILE;
+      if (it + 1 < my_tiles) xn = obj < md.n ? __ldg(md.x + obj) : 1.0e30f;
+      if (!mbar_wait(&mu_full[s], ph)) { fail = 1; break; }
+      tc_fence_after();
+      uint32_t v[8];
+      tmem_ld_x8(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
+      tmem_ld_wait();
+      const float muf = (__uint_as_float(v[0]) + __uint_as_float(v[1])) +
+                        __uint_as_float(v[2]);
+      // u = (x - x0) + W.theta ; zs_e = cs_e - ks*u
+      const float u = valid ? (xv - x0) + muf : 1.0e30f;
+      uint8_t* gs = s_g + s * 8192 + (o >> 6) * 4096;
+      const uint32_t ko = o & 63;
+      float zs[LL_ET], t[LL_ET], g[LL_ET], pp[LL_ET];
+#pragma unroll
+      for (int e = 0; e < LL_ET; ++e) zs[e] = fmaf(u, -ks, cs[e]);
+#pragma unroll
+      for (int e = 0; e < LL_ET; ++e)
+        t[e] = mgb_rcp(fmaf(fabsf(zs[e]), LL_HSCALE, 1.0f));
+#pragma unroll
+      for (int e = 0; e < LL_ET; ++e) g[e] = mgb_ex2(-(zs[e] * zs[e]));
+#pragma unroll
+      for (int e = 0; e < LL_ET; ++e)
+        pp[e] = fmaf(0.5f * MGB_ERFCX_C8, t[e], 0.5f * MGB_ERFCX_C7);
+#define LL_HORNER(C)                                            \
+  _Pragma("unroll") for (int e = 0; e < LL_ET; ++e) pp[e] =     \
+      fmaf(pp[e], t[e], 0.5f * (C));
+      LL_HORNER(MGB_ERFCX_C6)
+      LL_HORNER(MGB_ERFCX_C5)
+      LL_HORNER(MGB_ERFCX_C4)
+      LL_HORNER(MGB_ERFCX_C3)
+      LL_HORNER(MGB_ERFCX_C2)
+      LL_HORNER(MGB_ERFCX_C1)
+      LL_HORNER(MGB_ERFCX_C0)
+#undef LL_HORNER
+#pragma unroll
+      for (int e = 0; e < LL_ET; ++e) {
+        const float q = pp[e] * t[e] * g[e];
+        accT[e] += __uint_as_float(__float_as_uint(q) |
+                                   (~__float_as_uint(zs[e]) & 0x80000000u));
+        accO[e] += (int)(__float_as_uint(zs[e]) >> 31);
+        accZ[e] = fmaf(zs[e], g[e], accZ[e]);
+        // g -> two bf16 planes, rows (edge) and (16 + edge), column = object
+        const float ghi = bf16_val(g[e]);
+        const uint32_t r = (uint32_t)(e_first + e);
+        *reinterpret_cast<uint16_t*>(gs + sw128_offset_16b(r, ko)) =
+            bf16_bits(ghi);
+        *reinterpret_cast<uint16_t*>(gs + sw128_offset_16b(16u + r, ko)) =
+            bf16_bits(g[e] - ghi);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&g_full[s]);
+    }
+#pragma unroll
+    for (int e = 0; e < LL_ET; ++e) {
+      const float tt = mgb_warp_sum(accT[e]);
+      const float zz = mgb_warp_sum(accZ[e]);
+      const int oo = __reduce_add_sync(0xffffffffu, accO[e]);
+      if (lane == 0) {
+        s_warp[cw][3 * e + 0] = (double)tt;
+        s_warp[cw][3 * e + 1] = -(double)oo;   // objects below -> sign flip
+        s_warp[cw][3 * e + 2] = (double)zz;
+      }
+    }
+  }
+  if (fail) atomicExch(&s_fail, 1);
+  __syncthreads();
+
+  // ---- per-edge totals of T, O, Z (fp64) ---------------------------------
+  for (int j = tid; j < 3 * E; j += LL_THREADS) {
+    const int e = j / 3, q = j - 3 * e;
+    const int grp = e / LL_ET, el = e - grp * LL_ET;
+    double sacc = 0.0;
+    for (int w = 0; w < 4; ++w) sacc += s_warp[grp * 4 + w][3 * el + q];
+    s_edge[e][q] = sacc;
+  }
+  // ---- D2 (TMEM) -> shared: rows 0..15 g_hi, 16..31 g_lo, P columns -------
+  float* s_gw = reinterpret_cast<float*>(smem);   // pipeline buffers are dead
+  if (warp == 4) {   // warp 4 owns TMEM lanes 0..31
+    int okw = 1;
+    if (my_tiles > 0) okw = mbar_wait(&d2_done, 0);
+    tc_fence_after();
+    for (int c = 0; c < P; c += 16) {
+      uint32_t v[16];
+      if (my_tiles > 0) {
+        tmem_ld_x16(tm_d2 + c, v);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = 0u;
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i)
+        s_gw[lane * P + c + i] = __uint_as_float(v[i]);
+    }
+    if (!okw) atomicExch(&s_fail, 1);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 256);
+
+  // ---- per-CTA partial: [D_k][Zd_k][GWd_k,j] -------------------------------
+  for (int j = tid; j < M; j += LL_THREADS) {
+    double val;
+    if (j < K) {
+      const int k = j;
+      val = (s_edge[k + 1][1] - s_edge[k][1]) + (s_edge[k + 1][0] - s_edge[k][0]);
+    } else if (j < 2 * K) {
+      const int k = j - K;
+      val = s_edge[k + 1][2] - s_edge[k][2];
+    } else {
+      const int k = (j - 2 * K) / P, f = (j - 2 * K) - k * P;
+      const double hi1 = s_gw[(k + 1) * P + f], lo1 = s_gw[(17 + k) * P + f];
+      const double hi0 = s_gw[k * P + f], lo0 = s_gw[(16 + k) * P + f];
+      val = (hi1 - hi0) + (lo1 - lo0);
+    }
+    partials[(size_t)blockIdx.x * M + j] = val;
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned ticket = atomicAdd(counter, 1u);
+    s_is_last = (ticket == (unsigned)(G - 1));
+    if (s_fail) atomicExch(counter + 1, 1u);   // sticky pipeline-timeout flag
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+
+  // ---- fixed-order grid reduction (8 lanes per value) ---------------------
+  double* s_tot = reinterpret_cast<double*>(smem);            // M doubles
+  double* s_stage = s_tot + ((M + 15) & ~15);                  // W * M doubles
+  {
+    const int sub = tid & 7, grp8 = tid >> 3, ngrp = LL_THREADS >> 3;
+    for (int j0 = 0; j0 < M; j0 += ngrp) {
+      const int j = j0 + grp8;
+      double accd = 0.0;
+      if (j < M)
+        for (int c = sub; c < G; c += 8)
+          accd += __ldcg(partials + (size_t)c * M + j);
+      accd += __shfl_xor_sync(0xffffffffu, accd, 4);
+      accd += __shfl_xor_sync(0xffffffffu, accd, 2);
+      accd += __shfl_xor_sync(0xffffffffu, accd, 1);
+      if (j < M && sub == 0) s_tot[j] = accd;
+    }
+  }
+  if (tid == 0) *counter = 0u;
+  __syncthreads();
+  if (a.reduce && pt.world > 1) mgb_ll_allreduce_f64(pt, s_tot, s_stage, M);
+  __syncthreads();
+
+  // ---- epilogue: sumstats, loss, dL/ds, gradient, optimiser ---------------
+  __shared__ double s_dl[MGB_LIN_MAX_BINS], s_ck[MGB_LIN_MAX_BINS],
+      s_loss, s_gsig;
+  const double inv = 0.7071067811865476 / sigma_d;
+  const double rsqrtpi = 0.5641895835477563;
+  const double dsdp = md.sigma_link == 1 ? 2.302585092994046 * sigma_d : 1.0;
+  if (warp == 0) {
+    double s_k = 0.0, l_k = 0.0, dl_k = 0.0, dsg_k = 0.0;
+    if (lane < K) {
+      const double nrm = (double)md.norm[lane];
+      s_k = nrm * s_tot[lane];
+      dsg_k = -nrm * (rsqrtpi * 0.8325546111576977 / sigma_d) * dsdp *
+              s_tot[K + lane];
+      s_ck[lane] = -nrm * inv * rsqrtpi;     // d s_k / d theta_j = ck * GWd
+      if (a.out_sumstats) a.out_sumstats[lane] = (float)s_k;
+      if (a.out_jac) a.out_jac[(size_t)lane * NP + md.nfeat] = (float)dsg_k;
+      if (a.mode >= MGB_MODE_LOSS_GRAD) {
+        const double tgt = (double)md.target[lane];
+        if (md.loss_kind == 0) {
+          const double eps = (double)md.loss_eps;
+          const double r = log10(s_k + eps) - log10(tgt + eps);
+          l_k = r * r / K;
+          dl_k = 2.0 * r / (K * (s_k + eps) * 2.302585092994046);
+        } else if (md.loss_kind == 1) {
+          const double r = s_k - tgt;
+          l_k = r * r / K;
+          dl_k = 2.0 * r / K;
+        } else {
+          const double ie = (double)md.inv_err[lane];
+          const double r = (s_k - tgt) * ie;
+          l_k = r * r;
+          dl_k = 2.0 * r * ie;
+        }
+      }
+      s_dl[lane] = dl_k;
+    }
+    const double loss = mgb_warp_sum(l_k);
+    const double gsig = mgb_warp_sum(dl_k * dsg_k);
+    if (lane == 0) { s_loss = loss; s_gsig = gsig; }
+  }
+  __syncthreads();
+  if (a.out_jac)
+    for (int j = tid; j < K * md.nfeat; j += LL_THREADS) {
+      const int k = j / md.nfeat, f = j - k * md.nfeat;
+      a.out_jac[(size_t)k * NP + f] = (float)(s_ck[k] * s_tot[2 * K + k * P + f]);
+    }
+  if (a.mode < MGB_MODE_LOSS_GRAD) return;
+  if (tid == 0 && a.out_loss) a.out_loss[0] = (float)s_loss;
+  const int step = (a.mode >= MGB_MODE_ADAM) ? *a.opt_step : 0;
+  const int row = step - a.step_base;
+  if (tid < NP) {
+    double gd = 0.0;
+    if (tid < md.nfeat) {
+      for (int k = 0; k < K; ++k)
+        gd += s_dl[k] * s_ck[k] * s_tot[2 * K + k * P + tid];
+    } else {
+      gd = s_gsig;
+    }
+    const float grad = (float)gd;
+    if (a.out_grad) a.out_grad[tid] = grad;
+    if (a.mode == MGB_MODE_GD) {
+      const float p = a.opt_p[tid];
+      if (a.traj && row >= 0 && row < a.traj_rows)
+        a.traj[(size_t)row * NP + tid] = p;
+      a.opt_p[tid] = p - a.lr * grad;
+    } else if (a.mode == MGB_MODE_ADAM) {
+      const int kind = a.bound_kind ? a.bound_kind[tid] : 0;
+      const float lo = a.bound_lo ? a.bound_lo[tid] : 0.f;
+      const float hi = a.bound_hi ? a.bound_hi[tid] : 0.f;
+      const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
+      const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
+      const float p = a.opt_p[tid];
+      float u = a.opt_u[tid];
+      const float gi = grad * ll_bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
+      const float m = (1.0f - a.b1) * gi + a.b1 * a.opt_m[tid];
+      const float v = (1.0f - a.b2) * gi * gi + a.b2 * a.opt_v[tid];
+      u = u - a.lr * (m / c1) / (sqrtf(v / c2) + a.eps);
+      const float pn = ll_bound_inverse(kind, lo, hi, u);
+      a.opt_m[tid] = m; a.opt_v[tid] = v; a.opt_u[tid] = u; a.opt_p[tid] = pn;
+      if (a.traj && row + 1 >= 0 && row + 1 < a.traj_rows)
+        a.traj[(size_t)(row + 1) * NP + tid] = pn;
+    }
+  }
+  if (a.mode >= MGB_MODE_ADAM) {
+    __syncthreads();
+    if (tid == 0) {
+      if (a.loss_hist && row >= 0 && row < a.traj_rows)
+        a.loss_hist[row] = (float)s_loss;
+      *a.opt_step = step + 1;
+    }
+  }
+}
+
+int g_ll_sms[64] = {0};
+int ll_sm_count() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (dev >= 0 && dev < 64 && g_ll_sms[dev]) return g_ll_sms[dev];
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) !=
+      cudaSuccess)
+    return 0;
+  if (dev >= 0 && dev < 64) g_ll_sms[dev] = sms;
+  return sms;
+}
+
 }  // namespace
+
+extern "C" uint64_t mgb_linlink_scratch_bytes(int nbins, int pfeat) {
+  if (nbins < 1 || nbins > MGB_LIN_MAX_BINS || (pfeat != 64 && pfeat != 128))
+    return 0;
+  const uint64_t m = 2ull * nbins + (uint64_t)nbins * pfeat;
+  return 256ull + (uint64_t)ll_sm_count() * m * 8ull;
+}
+
+extern "C" int mgb_linlink_step(const MgbLinModel* model,
+                                const MgbLinArgs* args, const MgbPeerTable* pt,
+                                void* scratch, uint64_t scratch_bytes,
+                                void* stream) {
+  MGB_REQUIRE(model && args && scratch, MGB_EINVAL,
+              "mgb_linlink_step: null argument");
+  const MgbLinModel& md = *model;
+  const MgbLinArgs& a = *args;
+  MGB_REQUIRE(md.nbins >= 1 && md.nbins <= MGB_LIN_MAX_BINS, MGB_ETOOBIG,
+              "mgb_linlink_step: nbins=%d outside [1,%d]", md.nbins,
+              MGB_LIN_MAX_BINS);
+  MGB_REQUIRE(md.pfeat == 64 || md.pfeat == 128, MGB_EINVAL,
+              "mgb_linlink_step: pfeat must be 64 or 128 (got %d)", md.pfeat);
+  MGB_REQUIRE(md.nfeat >= 1 && md.nfeat <= md.pfeat, MGB_EINVAL,
+              "mgb_linlink_step: nfeat=%d outside [1,%d]", md.nfeat, md.pfeat);
+  MGB_REQUIRE(md.n >= 0 && md.w && (md.n == 0 || md.x), MGB_EINVAL,
+              "mgb_linlink_step: x / w is null");
+  MGB_REQUIRE(((uintptr_t)md.w & 15u) == 0, MGB_EINVAL,
+              "mgb_linlink_step: w must be 16-byte aligned");
+  MGB_REQUIRE(md.n < (1ll << 31), MGB_ETOOBIG,
+              "mgb_linlink_step: n must be below 2^31 objects per GPU");
+  MGB_REQUIRE(a.mode >= MGB_MODE_SUMSTATS_JAC && a.mode <= MGB_MODE_GD,
+              MGB_EINVAL, "mgb_linlink_step: bad mode %d", a.mode);
+  if (a.mode >= MGB_MODE_ADAM) {
+    MGB_REQUIRE(a.opt_p && a.opt_step, MGB_EINVAL,
+                "mgb_linlink_step: optimiser state missing");
+    if (a.mode == MGB_MODE_ADAM)
+      MGB_REQUIRE(a.opt_u && a.opt_m && a.opt_v, MGB_EINVAL,
+                  "mgb_linlink_step: Adam state missing");
+  } else {
+    MGB_REQUIRE(a.params != nullptr, MGB_EINVAL,
+                "mgb_linlink_step: params is null");
+  }
+  MgbPeerTable ptv;
+  if (pt) {
+    ptv = *pt;
+  } else {
+    memset(&ptv, 0, sizeof(ptv));
+    ptv.world = 1;
+  }
+  const int mvals = 2 * md.nbins + md.nbins * md.pfeat;
+  if (a.reduce && ptv.world > 1)
+    MGB_REQUIRE(ptv.world <= MGB_MAX_WORLD &&
+                    2u * (unsigned)mvals <= ptv.ll_units,
+                MGB_ETOOBIG,
+                "mgb_linlink_step: %d LL units needed, peer table has %u",
+                2 * mvals, ptv.ll_units);
+  const uint64_t need = mgb_linlink_scratch_bytes(md.nbins, md.pfeat);
+  MGB_REQUIRE(need > 0 && scratch_bytes >= need, MGB_ETOOBIG,
+              "mgb_linlink_step: scratch %llu < %llu bytes",
+              (unsigned long long)scratch_bytes, (unsigned long long)need);
+  CUtensorMap map;
+  // at least one full box so that the encoder accepts tiny catalogues
+  const uint64_t rows = md.n > 0 ? (uint64_t)md.n : 1;
+  int rc = make_w_map(&map, md.w, rows, (uint64_t)md.pfeat);
+  if (rc != MGB_OK) return rc;
+  const LinSmemLayout L = lin_smem_layout(md.pfeat);
+  // the epilogue reuses the pipeline buffers for the reduction staging
+  size_t smem = (size_t)L.total;
+  const size_t epi = ((size_t)((mvals + 15) & ~15) +
+                      (size_t)(ptv.world > 1 ? ptv.world : 0) * mvals) * 8 + 64;
+  if (epi > smem) smem = epi;
+  MGB_REQUIRE(smem <= 227 * 1024, MGB_ETOOBIG,
+              "mgb_linlink_step: %zu bytes of shared memory needed", smem);
+  unsigned* counter = reinterpret_cast<unsigned*>(scratch);
+  double* partials =
+      reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + 256);
+  const int grid = ll_sm_count();
+  MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_linlink_step: no CUDA device");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (md.pfeat == 64) {
+    MGB_CUDA_CHECK(cudaFuncSetAttribute(
+        linlink_step_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int)smem));
+    linlink_step_kernel<64><<<grid, LL_THREADS, smem, st>>>(
+        map, md, a, ptv, partials, counter);
+  } else {
+    MGB_CUDA_CHECK(cudaFuncSetAttribute(
+        linlink_step_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        (int)smem));
+    linlink_step_kernel<128><<<grid, LL_THREADS, smem, st>>>(
+        map, md, a, ptv, partials, counter);
+  }
+  MGB_CUDA_CHECK(cudaGetLastError());
+  return MGB_OK;
+}
 
 extern "C" int mgb_linlink_selftest(const void* w_bf16, const float* theta,
                                     const float* gmat, float* out_mu,

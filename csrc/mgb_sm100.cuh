@@ -52,12 +52,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: returns false if the barrier did not complete in time (a
-// pipeline bug must not hang the GPU box).
+// Bounded wait (2 s of wall clock): returns false if the barrier did not
+// complete in time -- a pipeline bug must not hang the GPU box.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
-  for (uint32_t it = 0; it < (1u << 26); ++it)
-    if (mbar_try_wait(bar, parity)) return true;
-  return false;
+  if (mbar_try_wait(bar, parity)) return true;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    for (int it = 0; it < 64; ++it)
+      if (mbar_try_wait(bar, parity)) return true;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 2000000000ull) return false;
+  }
 }
 
 // ----------------------------------------------------------------------- TMA

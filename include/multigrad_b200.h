@@ -171,6 +171,72 @@ int mgb_erfbin_step_static(const MgbErfBinModel* model,
                            void* stream);
 
 /* ------------------------------------------------------------------------
+ * Linear-link soft-binned statistic on the tensor cores (tcgen05 + TMEM +
+ * TMA).  mu_h = x_h + sum_j W[h][j] theta_j with per-object bf16 features W
+ * (row-major [n][pfeat], pfeat = 64 or 128, 16-byte aligned), sigma =
+ * link(params[nfeat]).  params = (theta_0 .. theta_{nfeat-1}, p_sigma).
+ * One launch streams W once (TMA), runs the forward product W.theta and the
+ * Jacobian contraction G^T.W as UMMA tiles accumulating in TMEM, evaluates
+ * erfc/exp on the CUDA cores, reduces over CTAs and GPUs and finishes with
+ * the same loss / gradient / Adam epilogue as mgb_erfbin_step.
+ * Replaces jax.vjp of a user sumstats function with a linear predictor
+ * (OnePointModel._vjp, multigrad/multigrad.py:508-538) + adam.py:52-68.
+ * ---------------------------------------------------------------------- */
+#define MGB_LIN_MAX_BINS 11
+#define MGB_LIN_MAX_FEAT 128
+
+typedef struct MgbLinModel {
+  const float* x;        /* [n] object coordinate                            */
+  const void* w;         /* [n][pfeat] bf16 features                         */
+  int64_t n;
+  int32_t nbins;         /* K <= MGB_LIN_MAX_BINS                            */
+  int32_t nfeat;         /* features in use (<= pfeat); nparams = nfeat + 1  */
+  int32_t pfeat;         /* padded row length of W: 64 or 128                */
+  int32_t sigma_link;    /* 0: sigma = p, 1: sigma = 10**p                   */
+  int32_t loss_kind;     /* as in MgbErfBinModel                             */
+  float loss_eps;
+  float x0;              /* centring constant                                */
+  float edges[MGB_LIN_MAX_BINS + 1];
+  float norm[MGB_LIN_MAX_BINS];
+  float target[MGB_LIN_MAX_BINS];
+  float inv_err[MGB_LIN_MAX_BINS];
+} MgbLinModel;
+
+typedef struct MgbLinArgs {
+  int32_t mode;             /* MGB_MODE_SUMSTATS_JAC .. MGB_MODE_GD          */
+  int32_t reduce;           /* 1: sum over the peer workspace                */
+  int32_t jac_at_params;
+  int32_t traj_rows;
+  int32_t step_base;
+  float lr, b1, b2, eps;
+  const float* params;      /* [nfeat+1] (modes 1-2)                         */
+  float* out_sumstats;      /* [K]                                           */
+  float* out_jac;           /* [K][nfeat+1] or NULL                          */
+  float* out_loss;          /* [1] or NULL                                   */
+  float* out_grad;          /* [nfeat+1] or NULL                             */
+  float* opt_p;             /* optimiser state, [nfeat+1] each               */
+  float* opt_u;
+  float* opt_m;
+  float* opt_v;
+  int32_t* opt_step;
+  float* traj;              /* [traj_rows][nfeat+1]                          */
+  float* loss_hist;
+  const int32_t* bound_kind; /* device arrays [nfeat+1] or NULL              */
+  const float* bound_lo;
+  const float* bound_hi;
+} MgbLinArgs;
+
+uint64_t mgb_linlink_scratch_bytes(int nbins, int pfeat);
+/* `scratch` must be zero-filled once before its first use. */
+int mgb_linlink_step(const MgbLinModel* model, const MgbLinArgs* args,
+                     const MgbPeerTable* pt, void* scratch,
+                     uint64_t scratch_bytes, void* stream);
+/* building-block check used by the tests (one tile through both UMMAs) */
+int mgb_linlink_selftest(const void* w_bf16, const float* theta,
+                         const float* gmat, float* out_mu, float* out_j,
+                         int* status_dev, int P, void* stream);
+
+/* ------------------------------------------------------------------------
  * K3 stand-alone: Adam / bound transforms on device vectors for the generic
  * (user-defined torch model) path.  Replaces jax_opt.adam's opt_update and
  * the jitted per-scalar transforms (multigrad/adam.py:52-68, 192-239).

@@ -294,6 +294,44 @@ def gpu_fused_step_uses_one_launch():
     assert torch.equal(tg, ts)
 
 
+@case
+def gpu_linear_link_world_invariance():
+    """Tensor-core linear-link model: multi-GPU loss / gradient / Adam
+    trajectory equal the single-process float32 CPU values."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.models import LinearLinkBinnedModel
+    n, F = 24_000, 9
+    g = torch.Generator().manual_seed(5)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    feat = torch.cat([torch.ones(n, 1), 0.3 * torch.randn(n, F - 1,
+                                                          generator=g)], 1)
+    theta = torch.cat([torch.tensor([-2.0]),
+                       0.05 * torch.randn(F - 1, generator=g),
+                       torch.tensor([0.2])])
+    edges = np.linspace(9, 10, 11)
+    ref = LinearLinkBinnedModel(x=x, features=feat, bin_edges=edges,
+                                volume=10.0 * n, comm=mg.Comm(None),
+                                device="cpu")
+    tgt = ref.calc_sumstats_from_params(theta)
+    ref.set_target(tgt)
+    sl = slice(*np.linspace(0, n, SIZE + 1).astype(int)[RANK:RANK + 2])
+    model = LinearLinkBinnedModel(x=x[sl].to(DEV), features=feat[sl].to(DEV),
+                                  bin_edges=edges, volume=10.0 * n,
+                                  target_sumstats=tgt)
+    p = theta + 0.04
+    loss, grad = model.calc_loss_and_grad_from_params(p)
+    rl, rg = ref.calc_loss_and_grad_from_params(p)
+    assert torch.allclose(loss.cpu(), rl, rtol=2e-4), (loss, rl)
+    assert torch.allclose(grad.cpu(), rg, rtol=2e-3,
+                          atol=2e-4 * float(rg.abs().max())), (grad, rg)
+    traj = model.run_adam(p, nsteps=10, learning_rate=0.01)
+    rt = ref.run_adam(p, nsteps=10, learning_rate=0.01)
+    assert torch.allclose(traj.cpu(), rt, atol=5e-4), (traj[-1], rt[-1])
+    blobs = COMM.allgather(traj.cpu().numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
+
+
 def main():
     only = sys.argv[1:] or list(CASES)
     results = {}

@@ -1,0 +1,139 @@
+"""Tensor-core linear-link kernel (csrc/linlink.cu) against a float64
+PyTorch autograd oracle of the same model (same bf16-rounded features)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import multigrad_b200 as mg
+from multigrad_b200.models import LinearLinkBinnedModel
+
+pytestmark = pytest.mark.gpu
+SELF = mg.Comm(None)
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+def make(n, F, k=10, seed=0, link="identity", **kw):
+    g = torch.Generator().manual_seed(seed)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    feat = torch.cat([torch.ones(n, 1),
+                      0.3 * torch.randn(n, F - 1, generator=g)], 1)
+    edges = np.linspace(9.0, 10.0, k + 1)
+    gpu = LinearLinkBinnedModel(x=x.to(dev()), features=feat.to(dev()),
+                                bin_edges=edges, volume=10.0 * max(n, 1),
+                                sigma_link=link, comm=SELF, device=dev(), **kw)
+    cpu = LinearLinkBinnedModel(x=x.double(), features=feat, bin_edges=edges,
+                                volume=10.0 * max(n, 1), sigma_link=link,
+                                comm=SELF, device="cpu", **kw)
+    theta = torch.cat([torch.tensor([-2.0]),
+                       0.05 * torch.randn(F - 1, generator=g),
+                       torch.tensor([0.2 if link == "identity" else -0.6])])
+    return gpu, cpu, theta
+
+
+def oracle(cpu, p):
+    p64 = p.double().clone().requires_grad_(True)
+    s = cpu.calc_partial_sumstats_from_params(p64)
+    jac = torch.autograd.functional.jacobian(
+        lambda q: cpu.calc_partial_sumstats_from_params(q), p.double())
+    return s.detach(), jac
+
+
+def test_selftest_building_blocks():
+    from multigrad_b200.ops import _lib
+    lib = _lib.load()
+    for P in (64, 128):
+        g = torch.Generator().manual_seed(P)
+        W = torch.randn(128, P, generator=g).to(torch.bfloat16).to(dev())
+        theta = torch.randn(P, generator=g).to(dev())
+        G = torch.rand(32, 128, generator=g).to(dev())
+        mu = torch.zeros(128, device=dev())
+        J = torch.zeros(32, P, device=dev())
+        status = torch.zeros(1, dtype=torch.int32, device=dev())
+        rc = lib.mgb_linlink_selftest(W.data_ptr(), theta.data_ptr(),
+                                      G.data_ptr(), mu.data_ptr(),
+                                      J.data_ptr(), status.data_ptr(), P, None)
+        torch.cuda.synchronize()
+        assert rc == 0 and int(status) == 0
+        mu_ref = W.double() @ theta.double()
+        J_ref = G.to(torch.bfloat16).double() @ W.double()
+        assert (mu.double() - mu_ref).abs().max() < 1e-5 * mu_ref.abs().max()
+        assert (J.double() - J_ref).abs().max() < 1e-5 * J_ref.abs().max()
+
+
+@pytest.mark.parametrize("n,F,k", [(128, 3, 10), (1000, 7, 10), (20_000, 33, 11),
+                                   (50_001, 64, 10), (30_000, 100, 5),
+                                   (0, 4, 3), (5, 2, 1)])
+def test_sumstats_and_jacobian_vs_fp64(n, F, k):
+    gpu, cpu, p = make(n, F, k)
+    s, jac = gpu.calc_sumstats_and_jac_from_params(p)
+    gpu.plan().check_pipeline()
+    so, jo = oracle(cpu, p)
+    assert s.shape == (k,) and jac.shape == (k, F + 1)
+    assert torch.allclose(s.double().cpu(), so, rtol=5e-6, atol=1e-12)
+    scale = float(jo.abs().max()) if n else 1.0
+    assert torch.allclose(jac.double().cpu(), jo, rtol=2e-4,
+                          atol=2e-5 * scale), (jac[:, :3], jo[:, :3])
+
+
+def test_loss_grad_and_log10_link():
+    gpu, cpu, p = make(40_000, 20, link="log10")
+    truth = p.clone()
+    tgt = gpu.calc_sumstats_from_params(truth)
+    gpu.set_target(tgt)
+    cpu.set_target(tgt.cpu())
+    q = truth + 0.03
+    loss, grad = gpu.calc_loss_and_grad_from_params(q)
+    q64 = q.double().clone().requires_grad_(True)
+    l64 = cpu.calc_loss_from_sumstats(cpu.calc_partial_sumstats_from_params(q64))
+    (g64,) = torch.autograd.grad(l64, q64)
+    assert abs(float(loss) - float(l64)) < 2e-4 * abs(float(l64))
+    assert torch.allclose(grad.double().cpu(), g64, rtol=1e-3,
+                          atol=1e-4 * float(g64.abs().max()))
+    assert torch.allclose(gpu.calc_dloss_dparams(q), grad)
+
+
+@pytest.mark.parametrize("bounds", [False, True])
+def test_fused_adam_matches_generic(bounds):
+    F = 6
+    gpu, cpu, p = make(30_000, F)
+    tgt = gpu.calc_sumstats_from_params(p)
+    gpu.set_target(tgt)
+    cpu32 = LinearLinkBinnedModel(
+        x=gpu.x.cpu(), features=gpu.features.cpu(), bin_edges=gpu._edges64,
+        volume=gpu.volume, target_sumstats=tgt.cpu(), comm=SELF, device="cpu")
+    guess = p + 0.05
+    pb = [(-5.0, 0.0)] + [None] * (F - 1) + [(0.01, None)] if bounds else None
+    traj, losses = gpu.run_adam(guess, nsteps=20, learning_rate=0.01,
+                                param_bounds=pb, return_loss=True)
+    rt, rl = cpu32.run_adam(guess, nsteps=20, learning_rate=0.01,
+                            param_bounds=pb, return_loss=True)
+    assert traj.shape == (21, F + 1)
+    assert torch.allclose(traj.cpu(), rt, atol=5e-4), (traj[-1], rt[-1])
+    assert torch.allclose(losses.cpu(), rl, rtol=5e-3, atol=1e-7)
+    gd = gpu.run_simple_grad_descent(guess, nsteps=5, learning_rate=1e-3)
+    rgd = cpu32.run_simple_grad_descent(guess, nsteps=5, learning_rate=1e-3)
+    assert torch.allclose(gd.params.cpu(), rgd.params, atol=2e-4)
+
+
+def test_constant_feature_reproduces_smf_model():
+    """One constant feature == the scalar-shift SMF model."""
+    from multigrad_b200.models import SMFModel, smf
+    data = smf.make_smf_data(10_000, comm=SELF, device=dev())
+    n = data["log_halo_masses"].numel()
+    lin = LinearLinkBinnedModel(
+        x=data["log_halo_masses"], features=torch.ones(n, 1, device=dev()),
+        bin_edges=np.linspace(9, 10, 11), volume=data["volume"],
+        target_sumstats=data["target_sumstats"], comm=SELF, device=dev())
+    ref = SMFModel(aux_data=data, comm=SELF, device=dev())
+    p = torch.tensor([-1.9, 0.3])
+    l1, g1 = lin.calc_loss_and_grad_from_params(p)
+    l2, g2 = ref.calc_loss_and_grad_from_params(p)
+    assert torch.allclose(l1, l2, rtol=1e-5)
+    assert torch.allclose(g1, g2, rtol=1e-4, atol=1e-6)
+    assert torch.allclose(data["target_sumstats"],
+                          lin.calc_sumstats_from_params([-2.0, 0.2]))

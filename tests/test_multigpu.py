@@ -13,7 +13,8 @@ from .test_distributed_cpu import CASES as CPU_CASES
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
 WORKER = Path(__file__).with_name("_dist_worker.py")
-CASES = CPU_CASES + ["gpu_allreduce_kernels", "gpu_fused_step_uses_one_launch"]
+CASES = CPU_CASES + ["gpu_allreduce_kernels", "gpu_fused_step_uses_one_launch",
+                     "gpu_linear_link_world_invariance"]
 
 
 def _worlds():
