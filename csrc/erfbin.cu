@@ -423,23 +423,9 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   if (!s_is_last) return;
   __threadfence();
 
-  // ---- fixed-order grid reduction: 8 lanes per value -----------------------
-  {
-    const int sub = tid & 7, grp = tid >> 3;
-    const int ngrp = nthreads >> 3;
-    for (int j0 = 0; j0 < MP; j0 += ngrp) {
-      const int j = j0 + grp;
-      double accd = 0.0;
-      if (j < MP) {
-        const double* src = partials + (size_t)b * G * MP + j;
-        for (int c = sub; c < G; c += 8) accd += __ldcg(src + (size_t)c * MP);
-      }
-      accd += __shfl_xor_sync(0xffffffffu, accd, 4);
-      accd += __shfl_xor_sync(0xffffffffu, accd, 2);
-      accd += __shfl_xor_sync(0xffffffffu, accd, 1);
-      if (j < MP && sub == 0) s_tot[j] = accd;
-    }
-  }
+  // ---- fixed-order grid reduction ------------------------------------------
+  mgb_grid_reduce_f64(partials + (size_t)b * G * MP, G, MP, s_tot, tid,
+                      nthreads);
   if (tid == 0) counters[b] = 0u;  // ready for the next launch
   __syncthreads();
 
@@ -793,4 +779,45 @@ extern "C" int mgb_erfbin_step_static(const MgbErfBinModel* model,
       cudaMemsetAsync(scratch, 0, counter_bytes, (cudaStream_t)stream));
   return mgb_erfbin_step(model, args, pt, scratch, MGB_STATIC_SCRATCH_BYTES,
                          stream);
+}
+
+// ---------------------------------------------------------------------------
+// Host-driven evaluation in one native call: pinned params -> device, fused
+// loss+gradient launch, loss+gradient -> pinned host buffer, stream sync.
+// This is the per-evaluation body of the L-BFGS-B line search (reference
+// multigrad/bfgs.py:72-77 + multigrad.py:508-538) and of any host-side
+// optimiser loop; doing it in C keeps the host cost at a few microseconds.
+// `params_host` (nparams floats) and `out_host` (1 + nparams floats: loss,
+// gradient) should be pinned; `d_params` / `d_out` are device staging buffers
+// of the same sizes.
+// ---------------------------------------------------------------------------
+extern "C" int mgb_erfbin_eval_host(const MgbErfBinModel* model,
+                                    const MgbPeerTable* pt,
+                                    const float* params_host, float* out_host,
+                                    float* d_params, float* d_out,
+                                    void* scratch, uint64_t scratch_bytes,
+                                    void* stream) {
+  MGB_REQUIRE(model && params_host && out_host && d_params && d_out,
+              MGB_EINVAL, "mgb_erfbin_eval_host: null argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int P = model->nparams;
+  MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
+              "mgb_erfbin_eval_host: nparams=%d outside [1,%d]", P,
+              MGB_MAX_PARAMS);
+  MGB_CUDA_CHECK(cudaMemcpyAsync(d_params, params_host, sizeof(float) * P,
+                                 cudaMemcpyHostToDevice, st));
+  MgbStepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mode = MGB_MODE_LOSS_GRAD;
+  a.batch = 1;
+  a.reduce = (pt && pt->world > 1) ? 1 : 0;
+  a.params = d_params;
+  a.out_loss = d_out;
+  a.out_grad = d_out + 1;
+  const int rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
+  if (rc != MGB_OK) return rc;
+  MGB_CUDA_CHECK(cudaMemcpyAsync(out_host, d_out, sizeof(float) * (1 + P),
+                                 cudaMemcpyDeviceToHost, st));
+  MGB_CUDA_CHECK(cudaStreamSynchronize(st));
+  return MGB_OK;
 }

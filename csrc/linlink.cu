@@ -606,20 +606,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   // ---- fixed-order grid reduction (8 lanes per value) ---------------------
   double* s_tot = reinterpret_cast<double*>(smem);            // M doubles
   double* s_stage = s_tot + ((M + 15) & ~15);                  // W * M doubles
-  {
-    const int sub = tid & 7, grp8 = tid >> 3, ngrp = LL_THREADS >> 3;
-    for (int j0 = 0; j0 < M; j0 += ngrp) {
-      const int j = j0 + grp8;
-      double accd = 0.0;
-      if (j < M)
-        for (int c = sub; c < G; c += 8)
-          accd += __ldcg(partials + (size_t)c * M + j);
-      accd += __shfl_xor_sync(0xffffffffu, accd, 4);
-      accd += __shfl_xor_sync(0xffffffffu, accd, 2);
-      accd += __shfl_xor_sync(0xffffffffu, accd, 1);
-      if (j < M && sub == 0) s_tot[j] = accd;
-    }
-  }
+  mgb_grid_reduce_f64(partials, G, M, s_tot, tid, LL_THREADS);
   if (tid == 0) *counter = 0u;
   __syncthreads();
   if (a.reduce && pt.world > 1) mgb_ll_allreduce_f64(pt, s_tot, s_stage, M);

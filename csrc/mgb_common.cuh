@@ -186,6 +186,38 @@ __device__ __forceinline__ float mgb_rcp(float x) {
   return y;
 }
 
+// Deterministic column sums of the per-CTA partials [G][M] (fp64, global) into
+// out[M] (shared), executed by a whole CTA after the last-CTA election.
+// 8 lanes share one value; every lane keeps 8 L2 loads in flight (a naive
+// dependent loop costs G/8 L2 round trips ~ 10 us for G = 296) and adds them
+// in a fixed order, then the 8 lanes are combined by a fixed shuffle tree.
+__device__ __forceinline__ void mgb_grid_reduce_f64(
+    const double* __restrict__ partials, int G, int M, double* out, int tid,
+    int nthreads) {
+  const int sub = tid & 7, grp = tid >> 3, ngrp = nthreads >> 3;
+  for (int j0 = 0; j0 < M; j0 += ngrp) {
+    const int j = j0 + grp;
+    double acc = 0.0;
+    if (j < M) {
+      const double* src = partials + j;
+      for (int c0 = sub; c0 < G; c0 += 64) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int c = c0 + 8 * u;
+          v[u] = c < G ? __ldcg(src + (size_t)c * M) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += v[u];
+      }
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    if (j < M && sub == 0) out[j] = acc;
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ T mgb_warp_sum(T v) {
 #pragma unroll

@@ -154,6 +154,15 @@ int mgb_erfbin_step(const MgbErfBinModel* model, const MgbStepArgs* args,
                     const MgbPeerTable* pt, void* scratch,
                     uint64_t scratch_bytes, void* stream);
 
+/* Host-driven evaluation in one call: params (pinned host) -> device, fused
+ * loss+gradient launch, (loss, grad) -> pinned host, stream sync.  The body of
+ * one L-BFGS-B line-search evaluation (reference multigrad/bfgs.py:72-77 plus
+ * multigrad.py:508-538).  out_host receives 1 + nparams floats. */
+int mgb_erfbin_eval_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
+                         const float* params_host, float* out_host,
+                         float* d_params, float* d_out, void* scratch,
+                         uint64_t scratch_bytes, void* stream);
+
 /* Same fused step, for callers that cannot allocate scratch (a plug-in that
  * only receives its input/output buffers from a host runtime, a process whose
  * device memory is owned by another pool, a phase in which calling the CUDA

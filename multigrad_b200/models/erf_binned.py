@@ -245,11 +245,11 @@ class ErfBinnedModel(OnePointModel):
     # --------------------------------------------------------- host fast path
     def loss_and_grad_host(self, params_host) -> "tuple[float, np.ndarray]":
         """Loss+gradient for host parameters with minimal host<->device
-        traffic: one pinned H2D copy of ``P`` floats, one launch, one pinned
-        D2H copy of ``1+P`` floats.  Used by ``run_bfgs`` and by the
-        end-to-end benchmark."""
-        from ..ops import _lib
-        from ..ops.erfbin import MODE_LOSS_GRAD
+        traffic, in ONE native call (``mgb_erfbin_eval_host``): pinned H2D
+        copy of ``P`` floats, the fused launch, pinned D2H copy of ``1+P``
+        floats, stream sync.  Used by ``run_bfgs`` and by the end-to-end
+        benchmark."""
+        import ctypes as C
         plan = self.plan()
         if self._host is None:
             P = self.nparams
@@ -258,20 +258,27 @@ class ErfBinnedModel(OnePointModel):
             d_in = torch.empty(P, dtype=torch.float32, device=self.device)
             d_out = torch.empty(1 + P, dtype=torch.float32,
                                 device=self.device)
-            a = _lib.MgbStepArgs()
-            a.mode, a.batch = MODE_LOSS_GRAD, 1
-            a.reduce = 1 if plan.world > 1 else 0
-            a.params = d_in.data_ptr()
-            a.out_loss = d_out.data_ptr()
-            a.out_grad = d_out.data_ptr() + 4
-            self._host = (h_in, h_out, d_in, d_out, a)
-        h_in, h_out, d_in, d_out, a = self._host
-        h_in.copy_(torch.as_tensor(np.asarray(params_host, dtype=np.float32)))
-        d_in.copy_(h_in, non_blocking=True)
-        plan.launch(a)
-        h_out.copy_(d_out, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        return float(h_out[0]), h_out[1:].double().numpy().copy()
+            scratch = plan._scratch_for(1)
+            self._host = (h_in, h_out, d_in, d_out, scratch, h_in.numpy(),
+                          h_out.numpy(),
+                          (C.byref(plan.model), plan._pt_ref,
+                           C.c_void_p(h_in.data_ptr()),
+                           C.c_void_p(h_out.data_ptr()),
+                           C.c_void_p(d_in.data_ptr()),
+                           C.c_void_p(d_out.data_ptr()),
+                           C.c_void_p(scratch.data_ptr()), scratch.numel()))
+        h = self._host
+        h[5][:] = params_host
+        if torch.cuda.current_device() != self.device.index:
+            torch.cuda.set_device(self.device)
+        rc = plan.lib.mgb_erfbin_eval_host(
+            *h[7], C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            from ..ops import _lib
+            _lib.check(rc, "mgb_erfbin_eval_host")
+        from ..ops import erfbin as _eb
+        _eb._LAUNCHES += 1
+        return float(h[6][0]), h[6][1:].astype(np.float64)
 
     # -------------------------------------------------------------- optimisers
     def run_adam(self, guess, nsteps=100, param_bounds=None,

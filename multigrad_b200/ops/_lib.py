@@ -191,6 +191,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.mgb_erfbin_step.argtypes = [C.POINTER(MgbErfBinModel),
                                     C.POINTER(MgbStepArgs),
                                     C.POINTER(MgbPeerTable), vp, u64, vp]
+    lib.mgb_erfbin_eval_host.argtypes = [C.POINTER(MgbErfBinModel),
+                                         C.POINTER(MgbPeerTable), vp, vp, vp,
+                                         vp, vp, u64, vp]
+    lib.mgb_erfbin_eval_host.restype = C.c_int
     lib.mgb_erfbin_step_static.argtypes = [C.POINTER(MgbErfBinModel),
                                            C.POINTER(MgbStepArgs),
                                            C.POINTER(MgbPeerTable), vp]

@@ -129,12 +129,14 @@ class ErfBinPlan:
     def launch(self, args: MgbStepArgs) -> None:
         global _LAUNCHES
         s = self._scratch_for(args.batch)
-        with torch.cuda.device(self.device):
-            rc = self.lib.mgb_erfbin_step(
-                C.byref(self.model), C.byref(args), self._pt_ref,
-                s.data_ptr(), s.numel(),
-                C.c_void_p(torch.cuda.current_stream().cuda_stream))
-        _lib.check(rc, "mgb_erfbin_step")
+        if torch.cuda.current_device() != self.device.index:
+            torch.cuda.set_device(self.device)     # one process per GPU
+        rc = self.lib.mgb_erfbin_step(
+            C.byref(self.model), C.byref(args), self._pt_ref,
+            s.data_ptr(), s.numel(),
+            C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc:
+            _lib.check(rc, "mgb_erfbin_step")
         _LAUNCHES += 1
 
     # ------------------------------------------------------- evaluation modes

@@ -26,9 +26,21 @@ for _ in range(5):
     plan.launch(a)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+graph = None
+if os.environ.get("KB_GRAPH"):
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        for _ in range(20):
+            plan.launch(a)
+    graph.replay()
+    torch.cuda.synchronize()
 e0.record()
-for _ in range(K):
-    plan.launch(a)
+if graph is not None:
+    for _ in range(K // 20):
+        graph.replay()
+else:
+    for _ in range(K):
+        plan.launch(a)
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / K
