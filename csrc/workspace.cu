@@ -73,3 +73,21 @@ extern "C" int mgb_ws_read_ctrl(const void* local_base, int idx, uint32_t* out,
   MGB_CUDA_CHECK(cudaStreamSynchronize(st));
   return MGB_OK;
 }
+
+// Byte offset of bulk region A inside a workspace block (region B follows at
+// + round_up(bulk_bytes, 1024)).
+extern "C" uint64_t mgb_ws_bulk_offset(int world, uint32_t ll_units) {
+  return mgb_bulk_off(world, ll_units);
+}
+
+// K7: device-to-device copy that also accepts peer-mapped (CUDA IPC) pointers,
+// i.e. a copy over NVLink when `src` lives in another rank's workspace.
+// Replaces the pickled send/recv of util.scatter_nd (multigrad/util.py:65-77).
+extern "C" int mgb_peer_copy(void* dst, const void* src, uint64_t bytes,
+                             void* stream) {
+  MGB_REQUIRE(dst && src, MGB_EINVAL, "mgb_peer_copy: null argument");
+  if (bytes == 0) return MGB_OK;
+  MGB_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice,
+                                 (cudaStream_t)stream));
+  return MGB_OK;
+}

@@ -57,6 +57,11 @@ int mgb_ws_free(void* ptr);
 int mgb_ws_export(void* ptr, uint8_t handle_out[64]);
 int mgb_ws_import(const uint8_t handle[64], void** out_ptr);
 int mgb_ws_unimport(void* ptr);
+uint64_t mgb_ws_bulk_offset(int world, uint32_t ll_units);
+/* K7: device-to-device copy that accepts peer-mapped pointers (NVLink copy);
+ * with the bulk region it replaces the pickled send/recv of util.scatter_nd
+ * (multigrad/util.py:65-77). */
+int mgb_peer_copy(void* dst, const void* src, uint64_t bytes, void* stream);
 /* reads ctrl word `idx` (0 epoch, 1 error, 2 bulk epoch) of a local block */
 int mgb_ws_read_ctrl(const void* local_base, int idx, uint32_t* out,
                      void* stream);

@@ -179,6 +179,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.mgb_ws_export.argtypes = [vp, C.c_char_p]
     lib.mgb_ws_import.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.mgb_ws_unimport.argtypes = [vp]
+    lib.mgb_ws_bulk_offset.restype = u64
+    lib.mgb_ws_bulk_offset.argtypes = [C.c_int, u32]
+    lib.mgb_peer_copy.restype = C.c_int
+    lib.mgb_peer_copy.argtypes = [vp, vp, u64, vp]
     lib.mgb_ws_read_ctrl.argtypes = [vp, C.c_int, C.POINTER(u32), vp]
     lib.mgb_allreduce_sum.argtypes = [C.POINTER(MgbPeerTable), vp, u64,
                                       C.c_int, C.c_int, vp]

@@ -157,13 +157,19 @@ def scatter_nd(array, axis: int = 0, comm=_DEFAULT, root: int = 0):
     """Scatter an n-d array from ``root``: rank ``i`` gets the ``i``-th of
     ``size`` near-even chunks along ``axis`` (reference ``util.py:65-77``).
 
-    Accepts numpy arrays or torch tensors on the root.  Chunks travel over the
-    cold-path (gloo) point-to-point channel; each rank then uploads its shard
-    to its own GPU with one pinned H2D copy (see ``utils.to_device_shard``).
+    Accepts numpy arrays or torch tensors on the root.  Host arrays travel
+    over the cold-path (gloo) point-to-point channel.  A CUDA tensor on the
+    root is scattered GPU-to-GPU over NVLink through the peer workspace (K7)
+    and arrives as a CUDA tensor on every rank.
     """
     comm = _resolve(comm)
     if comm is None or comm.size == 1:
         return array
+    on_device = comm.bcast(
+        isinstance(array, torch.Tensor) and array.is_cuda
+        if comm.rank == root else None, root=root)
+    if on_device:
+        return _scatter_nd_device(array, axis, comm, root)
     if comm.rank == root:
         if isinstance(array, torch.Tensor):
             splits = list(torch.tensor_split(array.cpu(), comm.size, dim=axis))
@@ -175,3 +181,53 @@ def scatter_nd(array, axis: int = 0, comm=_DEFAULT, root: int = 0):
                 comm.send(splits[i], dest=i)
         return ans
     return comm.recv(source=root)
+
+
+def _scatter_nd_device(array, axis, comm: Comm, root: int) -> torch.Tensor:
+    """K7: scatter a CUDA tensor living on ``root`` over NVLink.  The root
+    stages windows of the (axis-major, contiguous) array in the bulk region of
+    its peer workspace; every rank copies its part of the window straight from
+    the root's memory (``mgb_peer_copy``, a peer-to-peer cudaMemcpy)."""
+    import ctypes as C
+    ws = comm.workspace()
+    lib = ws.lib
+    if comm.rank == root:
+        arr = array.detach().movedim(axis, 0).contiguous()
+        meta = (tuple(arr.shape), arr.dtype)
+    else:
+        arr, meta = None, None
+    shape, dtype = comm.bcast(meta, root=root)
+    rows = shape[0]
+    row_bytes = int(np.prod(shape[1:], dtype=np.int64)) * \
+        torch.empty(0, dtype=dtype).element_size()
+    base, extra = divmod(rows, comm.size)       # np.array_split boundaries
+    lo = comm.rank * base + min(comm.rank, extra)
+    hi = lo + base + (1 if comm.rank < extra else 0)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    out = torch.empty((hi - lo,) + tuple(shape[1:]), dtype=dtype, device=dev)
+    my_lo, my_hi = lo * row_bytes, hi * row_bytes
+    window = int(ws.table.bulk_bytes)
+    off = int(lib.mgb_ws_bulk_offset(comm.size, ws.table.ll_units))
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    total = rows * row_bytes
+    for w0 in range(0, max(total, 1), max(window, 1)):
+        w1 = min(w0 + window, total)
+        if comm.rank == root and w1 > w0:
+            _check(lib.mgb_peer_copy(ws.table.base[root] + off,
+                                     arr.data_ptr() + w0, w1 - w0, stream))
+        torch.cuda.synchronize()
+        comm.Barrier()                      # window staged
+        a, b = max(w0, my_lo), min(w1, my_hi)
+        if b > a:
+            _check(lib.mgb_peer_copy(out.data_ptr() + (a - my_lo),
+                                     ws.table.base[root] + off + (a - w0),
+                                     b - a, stream))
+        torch.cuda.synchronize()
+        comm.Barrier()                      # window consumed
+    return out.movedim(0, axis) if axis else out
+
+
+def _check(rc):
+    if rc:
+        from ..ops import _lib
+        _lib.check(rc, "mgb_peer_copy")

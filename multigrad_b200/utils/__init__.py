@@ -1,2 +1,4 @@
-"""Host-side helpers: random keys, timing, clock sampling."""
+"""Host-side helpers: random keys, timing / NVTX, checkpoints."""
 from . import rng  # noqa: F401
+from . import timing  # noqa: F401
+from . import checkpoint  # noqa: F401

@@ -233,6 +233,22 @@ def experimental_scan_gd():
 
 
 @case
+def gpu_scatter_nd_over_nvlink():
+    """K7: scatter of a CUDA tensor from the root through peer memory."""
+    if DEV.type != "cuda":
+        return
+    full = torch.arange(11 * 5 * 3, dtype=torch.float32).reshape(11, 5, 3)
+    for axis in (0, 1):
+        mine = mg.scatter_nd(full.to(DEV) if RANK == 0 else None, axis=axis)
+        want = torch.tensor_split(full, SIZE, dim=axis)[RANK]
+        assert mine.is_cuda and torch.equal(mine.cpu(), want), (axis, mine)
+    big = torch.arange(3_000_000, dtype=torch.float64)
+    mine = mg.scatter_nd(big.to(DEV) if RANK == SIZE - 1 else None,
+                         root=SIZE - 1)
+    assert torch.equal(mine.cpu(), torch.tensor_split(big, SIZE)[RANK])
+
+
+@case
 def gpu_allreduce_kernels():
     """K5: LL and two-shot all-reduce vs an exact host sum; every rank must
     hold bit-identical results."""

@@ -238,3 +238,26 @@ def test_group_single_process_sums_models():
     assert isinstance(hash(group), int) and group == group
     single = mg.OnePointGroup(a)
     assert isinstance(single.models, tuple)
+
+
+def test_checkpoint_resume_roundtrip(tmp_path):
+    from multigrad_b200.utils import checkpoint, timing
+    tgt = torch.tensor([1.0, -2.0])
+    traj, losses, st = adam.run_adam(_quadratic(tgt), torch.zeros(2), None,
+                                     nsteps=7, learning_rate=0.05,
+                                     return_loss=True, return_state=True)
+    path = str(tmp_path / "ckpt.npz")
+    checkpoint.save_adam_checkpoint(path, traj, st, losses)
+    t2, st2, l2 = checkpoint.load_adam_checkpoint(path)
+    assert torch.equal(t2, traj) and st2.step == 7 and torch.equal(l2, losses)
+    resumed = adam.run_adam(_quadratic(tgt), t2[-1], None, nsteps=5,
+                            learning_rate=0.05, init_state=st2)
+    full = adam.run_adam(_quadratic(tgt), torch.zeros(2), None, nsteps=12,
+                         learning_rate=0.05)
+    assert torch.allclose(resumed[-1], full[-1], atol=1e-7)
+    timer = timing.StepTimer()
+    for _ in range(3):
+        with timer.step(), timing.nvtx_range("step"):
+            _quadratic(tgt)(torch.zeros(2), None)
+    assert len(timer.times_ms()) == 3
+    assert timing.device_time_ms(lambda: None, iters=2, warmup=1) >= 0.0
