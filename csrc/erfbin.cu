@@ -65,8 +65,8 @@ __device__ __forceinline__ float2 vfma(float2 a, float2 b, float2 c) {
 // kappa = sqrt(log2(e)): exp(-z^2) == 2^(-(kappa z)^2)
 #define EB_KAPPA 1.2011224087864498f
 #define EB_INV_KAPPA 0.8325546111576977
-// t = 1/(1 + 0.5 |z|) = 1/(1 + (0.5/kappa) |zs|)
-#define EB_HSCALE (0.5f / EB_KAPPA)
+// t = 1/(1 + c |z|) = 1/(1 + (c/kappa) |zs|), c = MGB_ERFCX_CSCALE
+#define EB_HSCALE (MGB_ERFCX_CSCALE / EB_KAPPA)
 #define EB_ZS_SKIP 12.4f  // |zs| beyond which g and q flush to zero
 
 // Per-edge accumulators are scalar: a packed FADD2 and two FADDs cost the
@@ -103,21 +103,17 @@ __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
     const float2 zz = vmul(zs[e], zs[e]);
     g[e] = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
   }
-  // Horner; coefficients pre-halved so that p = erfcx/2 / t
+  // Horner, stage by stage; coefficients pre-halved so that p = erfcx/2 / t
+  constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
   for (int e = 0; e < ET; ++e)
-    p[e] = vfma(f2s(0.5f * MGB_ERFCX_C8), t[e], f2s(0.5f * MGB_ERFCX_C7));
-#define EB_HORNER(C)                                         \
-  _Pragma("unroll") for (int e = 0; e < ET; ++e) p[e] =      \
-      vfma(p[e], t[e], f2s(0.5f * (C)));
-  EB_HORNER(MGB_ERFCX_C6)
-  EB_HORNER(MGB_ERFCX_C5)
-  EB_HORNER(MGB_ERFCX_C4)
-  EB_HORNER(MGB_ERFCX_C3)
-  EB_HORNER(MGB_ERFCX_C2)
-  EB_HORNER(MGB_ERFCX_C1)
-  EB_HORNER(MGB_ERFCX_C0)
-#undef EB_HORNER
+    p[e] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[e],
+                f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
+#pragma unroll
+  for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
+#pragma unroll
+    for (int e = 0; e < ET; ++e) p[e] = vfma(p[e], t[e], f2s(0.5f * kC[d]));
+  }
 #pragma unroll
   for (int e = 0; e < ET; ++e) p[e] = vmul(p[e], t[e]);
   if (WEIGHTED) {
@@ -348,6 +344,12 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   __shared__ double s_stage[MGB_MAX_WORLD * 3 * MGB_MAX_BINS];
   __shared__ int s_is_last;
 
+  // Programmatic dependent launch: this grid may have been scheduled while
+  // the previous step's last CTA was still in its epilogue (launch latency and
+  // CTA scheduling overlap with it).  Everything it wrote -- parameters,
+  // optimiser state, the ticket counter -- is visible after this wait.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
   // gated launch: uniform early exit on every rank (no ticket, no exchange)
   if (a.gate != nullptr && __ldg(a.gate) == 0.0f) return;
 
@@ -386,6 +388,8 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
           md, s_cs, e_first, ks, x0, wj, wpg, lane, s_warp[warp]);
     }
   }
+  // the object loop of this CTA is done: let the next step's grid be scheduled
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   __syncthreads();
 
   // ---- CTA reduction in fp64: per-edge totals, then bin differences --------
@@ -480,45 +484,44 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   const double loss = mgb_warp_sum(l_k);
   const double gmu = mgb_warp_sum(dl_k * dmu_k);
   const double gsg = mgb_warp_sum(dl_k * dsg_k);
-  if (lane != 0) return;
-
-  float grad[MGB_MAX_PARAMS];
-#pragma unroll
-  for (int i = 0; i < MGB_MAX_PARAMS; ++i) {
+  // lane i owns parameter i from here on (the warp sums left loss / gmu / gsg
+  // in every lane): the optimiser-state loads of all parameters are then in
+  // flight together instead of one dependent L2 round trip after another
+  const int i = lane;
+  const bool mine = i < P;
+  float grad = 0.f;
+  if (mine) {
     double v = 0.0;
     if (i == md.mu_idx) v += gmu;
     if (i == md.sig_idx) v += gsg;
-    grad[i] = (float)v;
+    grad = (float)v;
   }
-  if (a.out_loss) a.out_loss[b] = (float)loss;
-  if (a.out_grad)
-    for (int i = 0; i < P; ++i) a.out_grad[(size_t)b * P + i] = grad[i];
+  if (lane == 0 && a.out_loss) a.out_loss[b] = (float)loss;
+  if (mine && a.out_grad) a.out_grad[(size_t)b * P + i] = grad;
   if (a.mode < MGB_MODE_ADAM) return;
 
   // ---- optimiser update (replicated, deterministic on every GPU) ----------
   const int step = *a.opt_step;       // updates applied so far (bias corr.)
   const int row = step - a.step_base;  // row of this step in the buffers
-  if (a.loss_hist && row >= 0 && row < a.traj_rows)
+  if (lane == 0 && a.loss_hist && row >= 0 && row < a.traj_rows)
     a.loss_hist[row] = (float)loss;
-  if (a.mode == MGB_MODE_GD) {
-    for (int i = 0; i < P; ++i) {
+  if (mine) {
+    if (a.mode == MGB_MODE_GD) {
       const float p = a.opt_p[i];
       if (a.traj && row >= 0 && row < a.traj_rows)
         a.traj[(size_t)row * P + i] = p;
-      a.opt_p[i] = p - a.lr * grad[i];
-    }
-  } else {
-    const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
-    const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
-    for (int i = 0; i < P; ++i) {
-      const int kind = a.bound_kind[i];
-      const float lo = a.bound_lo[i], hi = a.bound_hi[i];
+      a.opt_p[i] = p - a.lr * grad;
+    } else {
       const float p = a.opt_p[i];
       float u = a.opt_u[i];
-      const float gi =
-          grad[i] * bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
-      const float m = (1.0f - a.b1) * gi + a.b1 * a.opt_m[i];
-      const float v = (1.0f - a.b2) * gi * gi + a.b2 * a.opt_v[i];
+      const float m0 = a.opt_m[i], v0 = a.opt_v[i];
+      const int kind = a.bound_kind[i];
+      const float lo = a.bound_lo[i], hi = a.bound_hi[i];
+      const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
+      const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
+      const float gi = grad * bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
+      const float m = (1.0f - a.b1) * gi + a.b1 * m0;
+      const float v = (1.0f - a.b2) * gi * gi + a.b2 * v0;
       const float mhat = m / c1, vhat = v / c2;
       u = u - a.lr * mhat / (sqrtf(vhat) + a.eps);
       const float pn = bound_inverse(kind, lo, hi, u);
@@ -530,7 +533,8 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
         a.traj[(size_t)(row + 1) * P + i] = pn;
     }
   }
-  *a.opt_step = step + 1;
+  __syncwarp();                       // every lane has read the step counter
+  if (lane == 0) *a.opt_step = step + 1;
 }
 
 typedef void (*eb_kernel_t)(const MgbErfBinModel, const MgbStepArgs,
@@ -686,8 +690,19 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   MGB_REQUIRE(k != nullptr, MGB_ESTATE,
               "mgb_erfbin_step: no kernel for %d edges per group", et_hi);
   dim3 g((unsigned)grid, (unsigned)a.batch, 1), blk(lay.nwarps * 32, 1, 1);
-  k<<<g, blk, 0, (cudaStream_t)stream>>>(md, a, ptv, lay, partials, counters);
-  MGB_CUDA_CHECK(cudaGetLastError());
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = g;
+  cfg.blockDim = blk;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  MGB_CUDA_CHECK(
+      cudaLaunchKernelEx(&cfg, k, md, a, ptv, lay, partials, counters));
   return MGB_OK;
 }
 

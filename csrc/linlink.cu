@@ -240,7 +240,7 @@ constexpr int LL_THREADS = 32 * (2 + LL_SETS * LL_CWARPS);   // 832
 constexpr int LL_ET = 4;            // edges per compute group (3 groups)
 constexpr int LL_MAXE = MGB_LIN_MAX_BINS + 1;
 constexpr float LL_KAPPA = 1.2011224087864498f;
-constexpr float LL_HSCALE = 0.5f / LL_KAPPA;
+constexpr float LL_HSCALE = MGB_ERFCX_CSCALE / LL_KAPPA;
 
 struct LinSmemLayout {
   int w_bytes, th_off, g_off, total;
@@ -474,20 +474,17 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         t[e] = mgb_rcp(fmaf(fabsf(zs[e]), LL_HSCALE, 1.0f));
 #pragma unroll
       for (int e = 0; e < LL_ET; ++e) g[e] = mgb_ex2(-(zs[e] * zs[e]));
+      constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
       for (int e = 0; e < LL_ET; ++e)
-        pp[e] = fmaf(0.5f * MGB_ERFCX_C8, t[e], 0.5f * MGB_ERFCX_C7);
-#define LL_HORNER(C)                                            \
-  _Pragma("unroll") for (int e = 0; e < LL_ET; ++e) pp[e] =     \
-      fmaf(pp[e], t[e], 0.5f * (C));
-      LL_HORNER(MGB_ERFCX_C6)
-      LL_HORNER(MGB_ERFCX_C5)
-      LL_HORNER(MGB_ERFCX_C4)
-      LL_HORNER(MGB_ERFCX_C3)
-      LL_HORNER(MGB_ERFCX_C2)
-      LL_HORNER(MGB_ERFCX_C1)
-      LL_HORNER(MGB_ERFCX_C0)
-#undef LL_HORNER
+        pp[e] = fmaf(0.5f * kC[MGB_ERFCX_DEG], t[e],
+                     0.5f * kC[MGB_ERFCX_DEG - 1]);
+#pragma unroll
+      for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
+#pragma unroll
+        for (int e = 0; e < LL_ET; ++e)
+          pp[e] = fmaf(pp[e], t[e], 0.5f * kC[d]);
+      }
 #pragma unroll
       for (int e = 0; e < LL_ET; ++e) {
         const float q = pp[e] * t[e] * g[e];
