@@ -362,15 +362,23 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
     }
   } else if (warp == 1) {
     // ------------------------------------------------------ UMMA issuer
-    if (lane == 0) {
+    // The whole warp runs the (warp-uniform) polling loop and one elected
+    // lane issues.  Descriptors are advanced by adding to their low word
+    // (start address >> 4): building them from scratch cost ~17 dependent
+    // uniform-datapath instructions per UMMA, which made this single thread
+    // the bottleneck of the kernel (~95 cycles per 32-cycle UMMA).
+    {
       const uint32_t id1 = idesc_bf16_f32(128, 16, false, false);
       // M = 64: only 32 rows of G are meaningful; the 64-row form halves the
       // operand fetch.  Its accumulator rows r land in TMEM lane
       // 32*(r/16) + r%16 (probed with tools/probe_m64.py).
       const uint32_t id2 = idesc_bf16_f32(64, P, false, true);
-      // Two event streams served by one thread: forward products are issued
-      // as soon as a W tile lands (up to LL_STAGES tiles ahead), Jacobian
-      // products as soon as the compute warps have published G for a tile.
+      const uint64_t dk = smem_desc_sw128(0, 16, 1024);                // K-major
+      const uint64_t dmn = smem_desc_sw128(0, LL_TILE * 128, 1024);    // MN-major
+      const uint64_t th0 = dk + (smem_u32(s_th) >> 4);
+      // Two event streams: forward products are issued as soon as a W tile
+      // lands (up to LL_STAGES tiles ahead), Jacobian products as soon as the
+      // compute warps have published G for a tile.
       long long n1 = 0, n2 = 0;
       unsigned long long t_idle = 0;
       while (n2 < my_tiles) {
@@ -380,16 +388,18 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
           const uint32_t ph = (uint32_t)((n1 / LL_STAGES) & 1);
           if (mbar_test_wait(&full_w[s], ph)) {
             tc_fence_after();
-            const uint32_t wb = smem_u32(s_w + s * L.w_bytes);
-            for (int kstep = 0; kstep < P / 16; ++kstep) {
-              const int fb = kstep >> 2, kk = kstep & 3;
-              const uint64_t da = smem_desc_sw128(
-                  wb + fb * LL_TILE * 128 + kk * 32, 16, 1024);
-              const uint64_t db = smem_desc_sw128(
-                  smem_u32(s_th + fb * 2048) + kk * 32, 16, 1024);
-              umma_bf16(tmem + s * 16, da, db, id1, kstep > 0);
+            if (elect_one()) {
+              const uint64_t a0 = dk + (smem_u32(s_w + s * L.w_bytes) >> 4);
+              const uint32_t d1 = tmem + s * 16;
+#pragma unroll
+              for (int kstep = 0; kstep < P / 16; ++kstep) {
+                const int fb = kstep >> 2, kk = kstep & 3;
+                umma_bf16(d1, a0 + (fb * (LL_TILE * 128 / 16) + kk * 2),
+                          th0 + (fb * (2048 / 16) + kk * 2), id1, kstep > 0);
+              }
+              umma_commit(&mu_full[s]);
             }
-            umma_commit(&mu_full[s]);
+            __syncwarp();
             ++n1;
             progressed = true;
           }
@@ -399,17 +409,20 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
           const uint32_t ph = (uint32_t)((n2 / LL_STAGES) & 1);
           if (mbar_test_wait(&g_full[s], ph)) {
             tc_fence_after();
-            const uint32_t wb = smem_u32(s_w + s * L.w_bytes);
-            const uint32_t gb = smem_u32(s_g + s * 8192);
-            for (int kstep = 0; kstep < LL_TILE / 16; ++kstep) {
-              const uint64_t da = smem_desc_sw128(
-                  gb + (kstep >> 2) * 4096 + (kstep & 3) * 32, 16, 1024);
-              const uint64_t db =
-                  smem_desc_sw128(wb + kstep * 2048, LL_TILE * 128, 1024);
-              umma_bf16(tm_d2 + (kstep % NACC) * P, da, db, id2,
-                        n2 > 0 || kstep >= NACC);
+            if (elect_one()) {
+              const uint64_t b0 = dmn + (smem_u32(s_w + s * L.w_bytes) >> 4);
+              const uint64_t a0 = dk + (smem_u32(s_g + s * 8192) >> 4);
+              const bool first = n2 == 0;
+#pragma unroll
+              for (int kstep = 0; kstep < LL_TILE / 16; ++kstep) {
+                umma_bf16(tm_d2 + (kstep % NACC) * P,
+                          a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
+                          b0 + kstep * (2048 / 16), id2,
+                          !first || kstep >= NACC);
+              }
+              umma_commit(&empty[s]);
             }
-            umma_commit(&empty[s]);
+            __syncwarp();
             ++n2;
             progressed = true;
           }
@@ -427,7 +440,8 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       // arrive, and a CTA without tiles would exit before it lands -- the
       // late arrive then hits whatever the next CTA keeps at that shared
       // memory address (seen as sporadic NaNs in the following launch).
-      if (my_tiles > 0) umma_commit(&d2_done);
+      if (my_tiles > 0 && elect_one()) umma_commit(&d2_done);
+      __syncwarp();
     }
   } else {
     // ------------------------------------------------------ compute warps
