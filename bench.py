@@ -82,7 +82,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "25"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -240,6 +240,21 @@ def main():
         ms_eval = timed(eval_step, K)
         extra["loss_grad_evals_per_sec"] = K / (ms_eval * 1e-3)
         extra["ms_per_eval"] = ms_eval / K
+        # --- run_bfgs end to end (config 3): scipy L-BFGS-B on rank 0, one
+        # fused loss+grad launch per line-search evaluation, parameters handed
+        # to the other GPUs by the device-side broadcast ---------------------
+        if not args.no_e2e:
+            sync_all()
+            t0 = time.perf_counter()
+            res = model.run_bfgs([-1.5, 0.35], maxsteps=40,
+                                 param_bounds=[(-4.0, 0.0), (0.05, 2.0)])
+            sync_all()
+            dt = max_over_ranks(time.perf_counter() - t0)
+            extra["run_bfgs"] = {
+                "nit": int(res.nit), "nfev": int(res.nfev),
+                "seconds": dt, "evals_per_sec": res.nfev / dt,
+                "x": [float(v) for v in res.x], "fun": float(res.fun),
+                "timing": "host wall clock, max over ranks"}
         # --- end to end through the public host API ---------------------------
         e2e = None
         if not args.no_e2e:
