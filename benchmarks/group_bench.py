@@ -7,9 +7,10 @@ The ranks are split with split_subcomms(ranks_per_group=[3, 3, 2]) (for 8
 GPUs; near-even otherwise); every group holds its own catalogue shard-ed over
 its GPUs and its own peer workspace.  One joint loss+gradient evaluation =
 one fused launch per GPU (in-kernel reduction inside the group) + one
-cross-group all-reduce of 1+P numbers over the world workspace.  Reports
-joint loss+grad evaluations per second and Adam steps per second
-(device-timed, max over ranks).  Reference counterpart: OnePointGroup
+cross-group all-reduce of 1+P numbers over the world workspace; an Adam step
+fuses that all-reduce with the replicated update (csrc/group.cu), so the fit
+never reads anything back.  Reports joint loss+grad evaluations per second
+and Adam steps per second (device-timed, max over ranks).  Reference counterpart: OnePointGroup
 (multigrad/multigrad.py:547-607) with its two pickled allgathers.
 """
 import argparse
@@ -65,14 +66,27 @@ def main():
 
     ms_eval = timed(lambda: group.calc_loss_and_grad_from_params(p),
                     args.steps)
-    torch.cuda.synchronize()
-    comm.Barrier()
-    e0, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
-    e0.record()
-    traj = group.run_adam(p, nsteps=args.steps, learning_rate=0.01)
-    e1.record()
-    torch.cuda.synchronize()
-    ms_adam = max(comm.allgather(e0.elapsed_time(e1) / args.steps))
+
+    def timed_fit(fit, nsteps):
+        fit(5)                                       # plans, workspaces
+        torch.cuda.synchronize()
+        comm.Barrier()
+        e0, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+        e0.record()
+        out = fit(nsteps)
+        e1.record()
+        torch.cuda.synchronize()
+        return out, max(comm.allgather(e0.elapsed_time(e1) / nsteps))
+
+    # device-resident: per step one fused launch per model + one fused
+    # cross-group reduce-and-update launch (csrc/group.cu)
+    traj, ms_adam = timed_fit(
+        lambda k: group.run_adam(p, nsteps=k, learning_rate=0.01), args.steps)
+    # the generic host-driven loop on the same group, for comparison
+    nh = max(args.steps // 4, 5)
+    _, ms_host = timed_fit(
+        lambda k: mg.OnePointModel.run_adam(group, p, nsteps=k,
+                                            learning_rate=0.01, comm=comm), nh)
     loss, grad = group.calc_loss_and_grad_from_params(traj[-1])
     if comm.rank == 0:
         print(json.dumps({
@@ -80,6 +94,7 @@ def main():
             "ranks_per_group": rpg, "halos_per_model": N,
             "ms_per_joint_eval": ms_eval, "joint_evals_per_sec": 1e3 / ms_eval,
             "ms_per_adam_step": ms_adam, "adam_steps_per_sec": 1e3 / ms_adam,
+            "host_driven_adam_steps_per_sec": 1e3 / ms_host,
             "final_params": traj[-1].cpu().tolist(), "final_loss": float(loss)}))
     comm.workspace().check_error()
     mg.shutdown()

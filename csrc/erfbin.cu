@@ -28,6 +28,7 @@
 #include <string.h>
 #include <mutex>
 #include "mgb_common.cuh"
+#include "mgb_opt.cuh"
 
 #define EB_SENTINEL_X 1.0e30f // padding object: contributes exactly zero
 
@@ -153,34 +154,6 @@ __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
     a[e].Z = fmaf(zs[e].x, g[e].x, a[e].Z);
     a[e].Z = fmaf(zs[e].y, g[e].y, a[e].Z);
   }
-}
-
-__device__ __forceinline__ float bound_inverse(int kind, float lo, float hi,
-                                               float u) {
-  if (kind == 1) {
-    const float mid = 0.5f * (hi + lo);
-    const float sc = (hi - lo) * 0.3183098861837907f;
-    return mid + sc * atanf(u / sc);
-  } else if (kind == 2) {
-    return 0.5f * (2.0f * lo + u + sqrtf(u * u + 4.0f));
-  } else if (kind == 3) {
-    return 0.5f * (2.0f * hi + u - sqrtf(u * u + 4.0f));
-  }
-  return u;
-}
-// d inverse(u)/du evaluated at u = x
-__device__ __forceinline__ float bound_jac(int kind, float lo, float hi,
-                                           float x) {
-  if (kind == 1) {
-    const float sc = (hi - lo) * 0.3183098861837907f;
-    const float r = x / sc;
-    return 1.0f / (1.0f + r * r);
-  } else if (kind == 2) {
-    return 0.5f * (1.0f + x / sqrtf(x * x + 4.0f));
-  } else if (kind == 3) {
-    return 0.5f * (1.0f - x / sqrtf(x * x + 4.0f));
-  }
-  return 1.0f;
 }
 
 // ---------------------------------------------------------------------------
@@ -505,34 +478,9 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   const int row = step - a.step_base;  // row of this step in the buffers
   if (lane == 0 && a.loss_hist && row >= 0 && row < a.traj_rows)
     a.loss_hist[row] = (float)loss;
-  if (mine) {
-    if (a.mode == MGB_MODE_GD) {
-      const float p = a.opt_p[i];
-      if (a.traj && row >= 0 && row < a.traj_rows)
-        a.traj[(size_t)row * P + i] = p;
-      a.opt_p[i] = p - a.lr * grad;
-    } else {
-      const float p = a.opt_p[i];
-      float u = a.opt_u[i];
-      const float m0 = a.opt_m[i], v0 = a.opt_v[i];
-      const int kind = a.bound_kind[i];
-      const float lo = a.bound_lo[i], hi = a.bound_hi[i];
-      const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
-      const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
-      const float gi = grad * bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
-      const float m = (1.0f - a.b1) * gi + a.b1 * m0;
-      const float v = (1.0f - a.b2) * gi * gi + a.b2 * v0;
-      const float mhat = m / c1, vhat = v / c2;
-      u = u - a.lr * mhat / (sqrtf(vhat) + a.eps);
-      const float pn = bound_inverse(kind, lo, hi, u);
-      a.opt_m[i] = m;
-      a.opt_v[i] = v;
-      a.opt_u[i] = u;
-      a.opt_p[i] = pn;
-      if (a.traj && row + 1 >= 0 && row + 1 < a.traj_rows)
-        a.traj[(size_t)(row + 1) * P + i] = pn;
-    }
-  }
+  if (mine)
+    mgb_opt_update_param(a, i, P, step, row, grad, a.bound_kind[i],
+                         a.bound_lo[i], a.bound_hi[i]);
   __syncwarp();                       // every lane has read the step counter
   if (lane == 0) *a.opt_step = step + 1;
 }

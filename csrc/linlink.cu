@@ -22,6 +22,7 @@
 #include <math.h>
 #include <string.h>
 #include "mgb_common.cuh"
+#include "mgb_opt.cuh"
 #include "mgb_sm100.cuh"
 
 using namespace sm100;
@@ -252,31 +253,6 @@ __host__ __device__ inline LinSmemLayout lin_smem_layout(int P) {
   L.g_off = L.th_off + (P / LL_FB) * 2048;
   L.total = L.g_off + ll_stages(P) * 8192 + 16384;  // + UMMA over-read slack
   return L;
-}
-
-__device__ __forceinline__ float ll_bound_inverse(int kind, float lo, float hi,
-                                                  float u) {
-  if (kind == 1) {
-    const float mid = 0.5f * (hi + lo), sc = (hi - lo) * 0.3183098861837907f;
-    return mid + sc * atanf(u / sc);
-  } else if (kind == 2) {
-    return 0.5f * (2.0f * lo + u + sqrtf(u * u + 4.0f));
-  } else if (kind == 3) {
-    return 0.5f * (2.0f * hi + u - sqrtf(u * u + 4.0f));
-  }
-  return u;
-}
-__device__ __forceinline__ float ll_bound_jac(int kind, float lo, float hi,
-                                              float x) {
-  if (kind == 1) {
-    const float sc = (hi - lo) * 0.3183098861837907f, r = x / sc;
-    return 1.0f / (1.0f + r * r);
-  } else if (kind == 2) {
-    return 0.5f * (1.0f + x / sqrtf(x * x + 4.0f));
-  } else if (kind == 3) {
-    return 0.5f * (1.0f - x / sqrtf(x * x + 4.0f));
-  }
-  return 1.0f;
 }
 
 template <int P>
@@ -683,28 +659,11 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
     }
     const float grad = (float)gd;
     if (a.out_grad) a.out_grad[tid] = grad;
-    if (a.mode == MGB_MODE_GD) {
-      const float p = a.opt_p[tid];
-      if (a.traj && row >= 0 && row < a.traj_rows)
-        a.traj[(size_t)row * NP + tid] = p;
-      a.opt_p[tid] = p - a.lr * grad;
-    } else if (a.mode == MGB_MODE_ADAM) {
-      const int kind = a.bound_kind ? a.bound_kind[tid] : 0;
-      const float lo = a.bound_lo ? a.bound_lo[tid] : 0.f;
-      const float hi = a.bound_hi ? a.bound_hi[tid] : 0.f;
-      const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
-      const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
-      const float p = a.opt_p[tid];
-      float u = a.opt_u[tid];
-      const float gi = grad * ll_bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
-      const float m = (1.0f - a.b1) * gi + a.b1 * a.opt_m[tid];
-      const float v = (1.0f - a.b2) * gi * gi + a.b2 * a.opt_v[tid];
-      u = u - a.lr * (m / c1) / (sqrtf(v / c2) + a.eps);
-      const float pn = ll_bound_inverse(kind, lo, hi, u);
-      a.opt_m[tid] = m; a.opt_v[tid] = v; a.opt_u[tid] = u; a.opt_p[tid] = pn;
-      if (a.traj && row + 1 >= 0 && row + 1 < a.traj_rows)
-        a.traj[(size_t)(row + 1) * NP + tid] = pn;
-    }
+    if (a.mode >= MGB_MODE_ADAM)
+      mgb_opt_update_param(a, tid, NP, step, row, grad,
+                           a.bound_kind ? a.bound_kind[tid] : 0,
+                           a.bound_lo ? a.bound_lo[tid] : 0.f,
+                           a.bound_hi ? a.bound_hi[tid] : 0.f);
   }
   if (a.mode >= MGB_MODE_ADAM) {
     __syncthreads();

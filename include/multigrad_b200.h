@@ -251,6 +251,27 @@ int mgb_linlink_selftest(const void* w_bf16, const float* theta,
                          int* status_dev, int P, void* stream);
 
 /* ------------------------------------------------------------------------
+ * K4 + K3: OnePointGroup step.  The member models' kernels leave their
+ * (loss, grad) on the device; this one launch sums the local contributions,
+ * all-reduces 1 + P doubles over the *main* communicator's peer workspace and
+ * applies the optimiser update (args->mode = MGB_MODE_ADAM / MGB_MODE_GD) or
+ * just writes the totals (MGB_MODE_LOSS_GRAD -> args->out_loss/out_grad).
+ * Replaces the pickled allgathers + host sum of the reference
+ * (multigrad/multigrad.py:560-581).  main_pt may be NULL (single process).
+ * ---------------------------------------------------------------------- */
+#define MGB_MAX_GROUP_MODELS 8
+typedef struct MgbGroupArgs {
+  int32_t n_models;         /* models evaluated by this rank                 */
+  int32_t nparams;          /* P <= MGB_MAX_PARAMS, shared by all models     */
+  int32_t active[MGB_MAX_GROUP_MODELS]; /* 1: this rank is the root of the
+                               model's sub-communicator and contributes      */
+  const float* loss[MGB_MAX_GROUP_MODELS];  /* [1] device                    */
+  const float* grad[MGB_MAX_GROUP_MODELS];  /* [P] device                    */
+} MgbGroupArgs;
+int mgb_group_step(const MgbGroupArgs* g, const MgbStepArgs* args,
+                   const MgbPeerTable* main_pt, void* stream);
+
+/* ------------------------------------------------------------------------
  * K3 stand-alone: Adam / bound transforms on device vectors for the generic
  * (user-defined torch model) path.  Replaces jax_opt.adam's opt_update and
  * the jitted per-scalar transforms (multigrad/adam.py:52-68, 192-239).

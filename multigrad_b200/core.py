@@ -325,9 +325,44 @@ class OnePointGroup:
         total = reduce_sum(packed, comm=self.main_comm)
         return total[0], total[1:]
 
+    # ------------------------------------------------- device-resident path
+    def _device_ok(self, params: torch.Tensor) -> bool:
+        """True when *every* member model on *every* rank of ``main_comm``
+        can evaluate device-resident (fused kernels with a built-in loss), so
+        that the fit can run through ``ops.group.GroupStepper``.  Collective
+        call: the ranks agree on the answer and all take the same path."""
+        ok = (params.is_cuda and params.numel() <= 8 and all(
+            getattr(m, "fused", False) and getattr(m, "_builtin_loss", False)
+            and hasattr(m, "device_loss_grad_launcher")
+            and m.device == params.device for m in self.models))
+        if self.main_comm is not None and self.main_comm.size > 1:
+            ok = all(self.main_comm.allgather(bool(ok)))
+        return bool(ok)
+
+    def _device_stepper(self, params: torch.Tensor):
+        from .ops.group import GroupStepper
+        return GroupStepper(self.models, self.main_comm, params)
+
     def run_simple_grad_descent(self, guess, nsteps=100, learning_rate=0.01):
-        return OnePointModel.run_simple_grad_descent(
-            self, guess, nsteps, learning_rate)
+        """Fixed-step gradient descent on the summed loss.  With fused member
+        models: per step one launch per model plus one fused
+        reduce-and-update launch (``csrc/group.cu``), nothing read back."""
+        p0 = self._params(guess)
+        if nsteps <= 0 or not self._device_ok(p0):
+            return OnePointModel.run_simple_grad_descent(
+                self, guess, nsteps, learning_rate)
+        from .ops.erfbin import FitState, MODE_GD
+        from .ops.group import fill_optimizer_args
+        from .ops._lib import MgbStepArgs
+        st = FitState(p0, p0, nsteps, p0.device, rows=max(nsteps, 1))
+        stepper = self._device_stepper(st.p)
+        args = fill_optimizer_args(MgbStepArgs(), MODE_GD, st, learning_rate)
+        for _ in range(nsteps):
+            stepper.step(args)
+        stepper.check_error()
+        return util.GradDescentResult(loss=st.loss_hist[:nsteps],
+                                      params=st.traj[:nsteps],
+                                      aux=[None] * nsteps)
 
     def run_bfgs(self, guess, maxsteps=100, param_bounds=None, randkey=None):
         return OnePointModel.run_bfgs(
@@ -336,10 +371,43 @@ class OnePointGroup:
 
     def run_adam(self, guess, nsteps=100, param_bounds=None,
                  learning_rate=0.01, randkey=None, const_randkey=False,
-                 **kw):
-        return OnePointModel.run_adam(
-            self, guess, nsteps, param_bounds, learning_rate, randkey,
-            const_randkey=const_randkey, comm=self.main_comm, **kw)
+                 reference_compat=True, init_state=None, return_state=False,
+                 return_loss=False):
+        """Adam on the summed loss (reference ``multigrad.py:591-599``).  With
+        fused member models the whole fit stays on the device: per step one
+        launch per model plus one fused reduce-and-update launch."""
+        p0 = self._params(guess)
+        if randkey is not None or nsteps <= 0 or not self._device_ok(p0):
+            return OnePointModel.run_adam(
+                self, guess, nsteps, param_bounds, learning_rate, randkey,
+                const_randkey=const_randkey, comm=self.main_comm,
+                reference_compat=reference_compat, init_state=init_state,
+                return_state=return_state, return_loss=return_loss)
+        from .ops.erfbin import FitState, MODE_ADAM
+        from .ops.group import fill_optimizer_args
+        from .ops._lib import MgbStepArgs
+        bounds, u0 = None, p0
+        if param_bounds is not None:
+            bounds = _adam.normalize_bounds(param_bounds, p0.numel())
+            u0 = _adam.apply_transforms(p0.cpu(), bounds).to(p0.device)
+        step0, m, v = 0, None, None
+        if init_state is not None:
+            step0, m, v = int(init_state.step), init_state.m, init_state.v
+        st = FitState(p0, u0, nsteps, p0.device, step0=step0, m=m, v=v)
+        st.traj[0].copy_(p0)
+        stepper = self._device_stepper(st.p)
+        args = fill_optimizer_args(MgbStepArgs(), MODE_ADAM, st,
+                                   learning_rate, bounds,
+                                   jac_at_params=reference_compat)
+        for _ in range(nsteps):
+            stepper.step(args)
+        stepper.check_error()
+        out = [st.traj]
+        if return_loss:
+            out.append(st.loss_hist[:nsteps])
+        if return_state:
+            out.append(_adam.AdamState(step0 + nsteps, st.m, st.v))
+        return out[0] if len(out) == 1 else tuple(out)
 
     def __hash__(self):
         return hash((self.main_comm.name, self.models[0]))

@@ -280,6 +280,33 @@ class ErfBinnedModel(OnePointModel):
         _eb._LAUNCHES += 1
         return float(h[6][0]), h[6][1:].astype(np.float64)
 
+    # ------------------------------------------------- device-resident driver
+    def device_loss_grad_launcher(self, params: torch.Tensor,
+                                  out: torch.Tensor):
+        """Zero-argument callable that enqueues ONE fused loss+gradient launch
+        reading the parameters from the CUDA tensor ``params`` (``[P]``, read
+        at execution time, not at call time) and writing ``(loss, grad)`` into
+        the CUDA tensor ``out`` (``[1 + P]``).  ``None`` when the model cannot
+        run that way (CPU, or a user-defined loss).  Used by
+        ``OnePointGroup``'s device-resident optimiser loop."""
+        if not (self.fused and self._builtin_loss):
+            return None
+        if self._target_t is None:
+            raise ValueError("no target_sumstats given")
+        from ..ops._lib import MgbStepArgs
+        from ..ops.erfbin import MODE_LOSS_GRAD
+        plan = self.plan()
+        a = MgbStepArgs()
+        a.mode, a.batch = MODE_LOSS_GRAD, 1
+        a.reduce = 1 if plan.world > 1 else 0
+        a.params = params.data_ptr()
+        a.out_loss = out.data_ptr()
+        a.out_grad = out.data_ptr() + 4
+
+        def launch(_keep=(params, out)):
+            plan.launch(a)
+        return launch
+
     # -------------------------------------------------------------- optimisers
     def run_adam(self, guess, nsteps=100, param_bounds=None,
                  learning_rate=0.01, randkey=None, const_randkey=False,

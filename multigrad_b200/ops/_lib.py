@@ -30,7 +30,7 @@ BUILD_DIR = ROOT / "build" / "obj"
 HASH_PATH = LIB_DIR / "libmgb200.hash"
 
 SOURCES = ["workspace.cu", "erfbin.cu", "allreduce.cu", "adam.cu",
-           "linlink.cu"]
+           "linlink.cu", "group.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
@@ -83,6 +83,18 @@ class MgbStepArgs(C.Structure):
         ("bound_kind", C.c_int32 * MGB_MAX_PARAMS),
         ("bound_lo", C.c_float * MGB_MAX_PARAMS),
         ("bound_hi", C.c_float * MGB_MAX_PARAMS),
+    ]
+
+
+MGB_MAX_GROUP_MODELS = 8
+
+
+class MgbGroupArgs(C.Structure):
+    _fields_ = [
+        ("n_models", C.c_int32), ("nparams", C.c_int32),
+        ("active", C.c_int32 * MGB_MAX_GROUP_MODELS),
+        ("loss", C.c_void_p * MGB_MAX_GROUP_MODELS),
+        ("grad", C.c_void_p * MGB_MAX_GROUP_MODELS),
     ]
 
 
@@ -207,6 +219,10 @@ def _declare(lib: C.CDLL) -> None:
         lib.mgb_linlink_selftest.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int,
                                              vp]
         lib.mgb_linlink_selftest.restype = C.c_int
+    lib.mgb_group_step.argtypes = [C.POINTER(MgbGroupArgs),
+                                   C.POINTER(MgbStepArgs),
+                                   C.POINTER(MgbPeerTable), vp]
+    lib.mgb_group_step.restype = C.c_int
     lib.mgb_adam_update.argtypes = [vp, vp, vp, vp, i32, i32, f32, f32, f32,
                                     f32, vp]
     lib.mgb_pointer_jump.argtypes = [vp, vp, i64, i32, C.POINTER(i32), vp, vp]

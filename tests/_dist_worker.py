@@ -311,6 +311,56 @@ def gpu_fused_step_uses_one_launch():
 
 
 @case
+def gpu_group_device_steps():
+    """K4+K3: OnePointGroup fits run device-resident (one fused
+    reduce-and-update launch per step over the main communicator) and agree
+    with the generic host-driven path."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.ops import group as gp
+    vols = [1.0, 1.7]
+    ngroups = 2 if SIZE > 1 else 1
+    sub, n, g = mg.split_subcomms(num_groups=ngroups)
+    full = smf.make_smf_data(30_000, comm=mg.Comm(None), device="cpu")
+    x_full = full["log_halo_masses"] + 0.05 * g
+    x_mine = torch.tensor_split(x_full, sub.size)[sub.rank].to(DEV)
+    mine = SMFModel(x=x_mine, bin_edges=full["smf_bin_edges"],
+                    volume=full["volume"] * vols[g],
+                    target_sumstats=full["target_sumstats"], comm=sub)
+    group = mg.OnePointGroup((mine,), main_comm=COMM)
+    p = torch.tensor([-1.95, 0.25])
+    bounds = [(-3.0, -1.0), (0.05, None)]
+    n0 = gp.launch_count()
+    traj, losses, state = group.run_adam(
+        p, nsteps=12, learning_rate=0.01, param_bounds=bounds,
+        return_loss=True, return_state=True)
+    torch.cuda.synchronize()
+    assert gp.launch_count() - n0 == 12
+    want, wl = mg.OnePointModel.run_adam(
+        group, p, nsteps=12, learning_rate=0.01, param_bounds=bounds,
+        comm=COMM, return_loss=True)
+    assert torch.allclose(traj.cpu(), want.cpu(), rtol=2e-5, atol=2e-6), \
+        (traj, want)
+    assert torch.allclose(losses.cpu(), wl.cpu(), rtol=2e-4, atol=1e-7)
+    blobs = COMM.allgather(traj.cpu().numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
+    # resuming from the returned state continues the same trajectory
+    ta, sa = group.run_adam(p, nsteps=6, learning_rate=0.01,
+                            param_bounds=bounds, return_state=True)
+    tb = group.run_adam(ta[-1], nsteps=6, learning_rate=0.01,
+                        param_bounds=bounds, init_state=sa)
+    assert torch.allclose(tb[-1].cpu(), traj[-1].cpu(), rtol=1e-5, atol=1e-6)
+    gd = group.run_simple_grad_descent(p, nsteps=5, learning_rate=1e-3)
+    gw = mg.OnePointModel.run_simple_grad_descent(group, p, nsteps=5,
+                                                  learning_rate=1e-3)
+    assert torch.allclose(gd.params.cpu(), torch.as_tensor(gw.params).cpu(),
+                          rtol=2e-5, atol=2e-6)
+    assert torch.allclose(gd.loss.cpu(), torch.as_tensor(gw.loss).cpu(),
+                          rtol=2e-4)
+    COMM.workspace().check_error() if SIZE > 1 else None
+
+
+@case
 def gpu_linear_link_world_invariance():
     """Tensor-core linear-link model: multi-GPU loss / gradient / Adam
     trajectory equal the single-process float32 CPU values."""

@@ -241,6 +241,36 @@ def test_fused_gd_matches_generic():
     assert torch.allclose(r.loss.cpu(), rr.loss, rtol=2e-3, atol=1e-8)
 
 
+@pytest.mark.parametrize("bounds", [None, [(-5.0, 0.0), (0.01, None)]])
+def test_group_device_steps_match_generic(bounds):
+    """K4+K3 on one GPU: two models in one OnePointGroup, device-resident
+    Adam / GD against the generic host-driven loop on the same group."""
+    from multigrad_b200.ops import group as gp
+    m1, *_ = make(n=20_000, k=10, seed=1)
+    m2, *_ = make(n=15_000, k=8, seed=2, lo=9.2, hi=10.2)
+    m1.set_target(m1.calc_sumstats_from_params([-2.0, 0.2]))
+    m2.set_target(m2.calc_sumstats_from_params([-2.0, 0.2]))
+    group = mg.OnePointGroup((m1, m2), main_comm=SELF)
+    guess = [-1.8, 0.3]
+    n0 = gp.launch_count()
+    traj, losses = group.run_adam(guess, nsteps=15, learning_rate=0.02,
+                                  param_bounds=bounds, return_loss=True)
+    assert gp.launch_count() - n0 == 15
+    want, wl = mg.OnePointModel.run_adam(
+        group, guess, nsteps=15, learning_rate=0.02, param_bounds=bounds,
+        comm=SELF, return_loss=True)
+    assert traj.shape == (16, 2)
+    assert torch.allclose(traj.cpu(), want.cpu(), rtol=2e-5, atol=2e-6)
+    assert torch.allclose(losses.cpu(), wl.cpu(), rtol=2e-4, atol=1e-8)
+    gd = group.run_simple_grad_descent(guess, nsteps=6, learning_rate=1e-3)
+    gw = mg.OnePointModel.run_simple_grad_descent(group, guess, nsteps=6,
+                                                  learning_rate=1e-3)
+    assert torch.allclose(gd.params.cpu(), torch.as_tensor(gw.params).cpu(),
+                          rtol=2e-5, atol=2e-6)
+    assert torch.allclose(gd.loss.cpu(), torch.as_tensor(gw.loss).cpu(),
+                          rtol=2e-4)
+
+
 def test_bfgs_tutorial_on_gpu():
     # docs/source/notebooks/intro.ipynb:258-281 through the fused kernel
     x = torch.log10(smf.load_halo_masses_tutorial(10_000, comm=SELF))
