@@ -27,11 +27,51 @@
 
 using namespace sm100;
 
+#ifdef LL_TRACE
+// Debug-only pipeline trace (tools/linlink_trace.py): SM-clock stamps of the
+// pipeline events of CTA 0 for LL_TRACE_N tiles starting at LL_TRACE_T0.
+#define LL_TRACE_N 256
+#define LL_TRACE_T0 300
+__device__ long long g_ll_trace[8][LL_TRACE_N];
+#define LL_TR(ev, tile)                                                       \
+  do {                                                                        \
+    const long long _t = (tile) - LL_TRACE_T0;                                \
+    if (blockIdx.x == 0 && _t >= 0 && _t < LL_TRACE_N)                        \
+      g_ll_trace[ev][_t] = clock64();                                         \
+  } while (0)
+__device__ long long g_ll_trace_w[24][2][LL_TRACE_N];   // per compute warp
+#define LL_TRW(cw, ev, tile)                                                  \
+  do {                                                                        \
+    const long long _t = (tile) - LL_TRACE_T0;                                \
+    if (blockIdx.x == 0 && _t >= 0 && _t < LL_TRACE_N)                        \
+      g_ll_trace_w[cw][ev][_t] = clock64();                                   \
+  } while (0)
+extern "C" int mgb_linlink_trace_read(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_ll_trace, sizeof(g_ll_trace));
+}
+extern "C" int mgb_linlink_trace_read_warps(long long* host) {
+  return (int)cudaMemcpyFromSymbol(host, g_ll_trace_w, sizeof(g_ll_trace_w));
+}
+#else
+#define LL_TR(ev, tile) do {} while (0)
+#define LL_TRW(cw, ev, tile) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int LL_TILE = 128;     // objects per tile (UMMA M of #1, K of #2)
 constexpr int LL_FB = 64;        // features per 128-byte swizzle block
 constexpr int LL_GROWS = 32;     // rows of G: 16 x g_hi, 16 x g_lo
+
+#ifndef LL_IDLE_SLEEP_NS
+#define LL_IDLE_SLEEP_NS 0
+#endif
+#ifndef LL_ABL
+#define LL_ABL 0   // ablation bits for tuning experiments (0 in production)
+#endif
+#ifndef LL_L2_PROMOTION
+#define LL_L2_PROMOTION CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+#endif
 
 // cuTensorMapEncodeTiled through the runtime (no link-time libcuda symbol)
 typedef CUresult (*encode_fn_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
@@ -68,7 +108,7 @@ int make_w_map(CUtensorMap* map, const void* w, uint64_t H, uint64_t P) {
   const CUresult r =
       enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w), gdim,
           gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+          CU_TENSOR_MAP_SWIZZLE_128B, LL_L2_PROMOTION,
           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MGB_REQUIRE(r == CUDA_SUCCESS, MGB_ESTATE,
               "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
@@ -284,8 +324,16 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   const int NP = md.nfeat + 1;
   const int M = 2 * K + K * P;     // doubles per CTA partial
   const long long ntiles = (md.n + LL_TILE - 1) / LL_TILE;
+#ifdef LL_CONTIG
+  const long long per_cta = (ntiles + G - 1) / G;
+  const long long tile0 = (long long)blockIdx.x * per_cta, tstride = 1;
+  const long long my_tiles =
+      ntiles > tile0 ? (ntiles - tile0 < per_cta ? ntiles - tile0 : per_cta) : 0;
+#else
+  const long long tile0 = blockIdx.x, tstride = G;
   const long long my_tiles =
       ntiles > blockIdx.x ? (ntiles - blockIdx.x + G - 1) / G : 0;
+#endif
 
   const float* pv = (a.mode >= MGB_MODE_ADAM) ? a.opt_p : a.params;
   const float p_sg = pv[md.nfeat];
@@ -329,7 +377,8 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         const int s = (int)(it % LL_STAGES);
         const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
         if (!mbar_wait(&empty[s], ph ^ 1u)) { fail = 1; break; }
-        const long long tile = blockIdx.x + it * G;
+        LL_TR(0, it);
+        const long long tile = tile0 + it * tstride;
         mbar_arrive_expect_tx(&full_w[s], (uint32_t)L.w_bytes);
         for (int fb = 0; fb < NFB; ++fb)
           tma_load_2d(s_w + s * L.w_bytes + fb * LL_TILE * 128, &wmap,
@@ -363,17 +412,19 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
           const int s = (int)(n1 % LL_STAGES);
           const uint32_t ph = (uint32_t)((n1 / LL_STAGES) & 1);
           if (mbar_test_wait(&full_w[s], ph)) {
+            LL_TR(1, n1);
             tc_fence_after();
             if (elect_one()) {
               const uint64_t a0 = dk + (smem_u32(s_w + s * L.w_bytes) >> 4);
               const uint32_t d1 = tmem + s * 16;
 #pragma unroll
-              for (int kstep = 0; kstep < P / 16; ++kstep) {
+              for (int kstep = 0; kstep < ((LL_ABL & 8) ? 0 : P / 16); ++kstep) {
                 const int fb = kstep >> 2, kk = kstep & 3;
                 umma_bf16(d1, a0 + (fb * (LL_TILE * 128 / 16) + kk * 2),
                           th0 + (fb * (2048 / 16) + kk * 2), id1, kstep > 0);
               }
               umma_commit(&mu_full[s]);
+              LL_TR(6, n1);
             }
             __syncwarp();
             ++n1;
@@ -384,19 +435,22 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
           const int s = (int)(n2 % LL_STAGES);
           const uint32_t ph = (uint32_t)((n2 / LL_STAGES) & 1);
           if (mbar_test_wait(&g_full[s], ph)) {
+            LL_TR(4, n2);
             tc_fence_after();
             if (elect_one()) {
               const uint64_t b0 = dmn + (smem_u32(s_w + s * L.w_bytes) >> 4);
               const uint64_t a0 = dk + (smem_u32(s_g + s * 8192) >> 4);
               const bool first = n2 == 0;
 #pragma unroll
-              for (int kstep = 0; kstep < LL_TILE / 16; ++kstep) {
+              for (int kstep = 0; kstep < ((LL_ABL & 1) ? 0 : LL_TILE / 16);
+                   ++kstep) {
                 umma_bf16(tm_d2 + (kstep % NACC) * P,
                           a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
                           b0 + kstep * (2048 / 16), id2,
                           !first || kstep >= NACC);
               }
               umma_commit(&empty[s]);
+              LL_TR(7, n2);
             }
             __syncwarp();
             ++n2;
@@ -410,6 +464,9 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
           if (t_idle == 0) t_idle = now;
           else if (now - t_idle > 2000000000ull) { fail = 1; break; }
+          // do not steal issue slots from the compute warps that share this
+          // SM sub-partition while there is nothing to issue
+          if (LL_IDLE_SLEEP_NS > 0) __nanosleep(LL_IDLE_SLEEP_NS);
         }
       }
       // Only when somebody will wait for it: a commit is an *asynchronous*
@@ -435,21 +492,30 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       cs[e] = (e_first + e < E) ? s_cs[e_first + e] : 3.0e18f;
       accT[e] = 0.f; accZ[e] = 0.f; accO[e] = 0;
     }
-    long long obj = ((long long)blockIdx.x + (long long)set * G) * LL_TILE + o;
-    float xn = (set < my_tiles && obj < md.n) ? __ldg(md.x + obj) : 1.0e30f;
+    long long obj = (tile0 + (long long)set * tstride) * LL_TILE + o;
+    float xn = (set < my_tiles && obj < md.n && !(LL_ABL & 16))
+                   ? __ldg(md.x + obj) : 1.0e30f;
     for (long long it = set; it < my_tiles; it += LL_SETS) {
       const int s = (int)(it % LL_STAGES);
       const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
       const float xv = xn;
       const bool valid = obj < md.n;
-      obj += (long long)LL_SETS * G * LL_TILE;
+      obj += (long long)LL_SETS * tstride * LL_TILE;
       if (it + LL_SETS < my_tiles)
-        xn = obj < md.n ? __ldg(md.x + obj) : 1.0e30f;
+        xn = (obj < md.n && !(LL_ABL & 16)) ? __ldg(md.x + obj) : 1.0e30f;
+      if (grp == 0 && quad == 0 && lane == 0) LL_TR(5, it);
       if (!mbar_wait(&mu_full[s], ph)) { fail = 1; break; }
+      if (grp == 0 && quad == 0 && lane == 0) LL_TR(2, it);
+      if (lane == 0) LL_TRW(cw, 0, it);
       tc_fence_after();
       uint32_t v[8];
-      tmem_ld_x8(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
-      tmem_ld_wait();
+      if (LL_ABL & 32) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0u;
+      } else {
+        tmem_ld_x8(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
+        tmem_ld_wait();
+      }
       const float muf = (__uint_as_float(v[0]) + __uint_as_float(v[1])) +
                         __uint_as_float(v[2]);
       // u = (x - x0) + W.theta ; zs_e = cs_e - ks*u
@@ -457,6 +523,14 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       uint8_t* gs = s_g + s * 8192 + (o >> 6) * 4096;
       const uint32_t ko = o & 63;
       float zs[LL_ET], t[LL_ET], g[LL_ET], pp[LL_ET];
+      if (LL_ABL & 4) {            // no math, no G stores: hand the tile on
+        accT[0] += u;
+        if (!(LL_ABL & 64)) fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&g_full[s]);
+        continue;
+      }
 #pragma unroll
       for (int e = 0; e < LL_ET; ++e) zs[e] = fmaf(u, -ks, cs[e]);
 #pragma unroll
@@ -495,13 +569,16 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         // element order in memory: column ko (even lane) then ko+1 (odd lane)
         const uint32_t word = odd ? ((other & 0xffffu) | (mine << 16))
                                   : ((mine >> 16) | (other & 0xffff0000u));
-        *reinterpret_cast<uint32_t*>(
-            gs + sw128_offset_16b(odd ? 16u + r : r, ko & ~1u)) = word;
+        if (!(LL_ABL & 2))
+          *reinterpret_cast<uint32_t*>(
+              gs + sw128_offset_16b(odd ? 16u + r : r, ko & ~1u)) = word;
       }
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&g_full[s]);
+      if (grp == 0 && quad == 0 && lane == 0) LL_TR(3, it);
+      if (lane == 0) LL_TRW(cw, 1, it);
     }
 #pragma unroll
     for (int e = 0; e < LL_ET; ++e) {

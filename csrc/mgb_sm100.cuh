@@ -41,8 +41,25 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar,
                "r"(bytes)
                : "memory");
 }
+// The suspend-time hint lets the hardware park the thread until the phase
+// completes (or the hint expires) instead of returning after the short default
+// limit: in the linear-link kernel 24 consumer warps re-polling every few
+// dozen cycles made up a quarter of all issued instructions and kept the
+// shared-memory pipe busy enough to delay the TMA writes (tools/linlink_trace.py).
+#ifndef MGB_MBAR_SUSPEND_NS
+#define MGB_MBAR_SUSPEND_NS 4000
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
+#if MGB_MBAR_SUSPEND_NS > 0
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"((uint32_t)MGB_MBAR_SUSPEND_NS)
+      : "memory");
+#else
   asm volatile(
       "{\n\t.reg .pred P;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
@@ -50,6 +67,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
+#endif
   return ok != 0;
 }
 // Non-blocking probe (try_wait may suspend the thread for a while, which is
