@@ -28,6 +28,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=float, default=64)
     ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--all-algos", action="store_true",
+                    help="also time every algorithm forced (LL / one-shot "
+                         "push / two-shot) to locate the crossovers")
     args = ap.parse_args()
     comm = mg.COMM
     dev = mg.parallel.local_device()
@@ -55,18 +58,42 @@ def main():
         return max(comm.allgather(us))
 
     rows = []
+    mc_x = None
+    if args.all_algos and comm.workspace().multicast():
+        mc_x = comm.workspace().multicast_tensor(
+            min(max(sizes), comm.workspace().multicast().bytes // 4))
     for n in sizes:
         x = torch.randn(n, device=dev)
         iters = args.iters if n < (1 << 22) else max(10, args.iters // 5)
         ours = timed(lambda: ar.all_reduce_sum_(x, comm), iters)
         nccl = timed(lambda: dist.all_reduce(x, group=comm.group), iters)
+        forced = {}
+        half = (int(comm.workspace().table.bulk_bytes) // 2) & ~1023
+        if args.all_algos and n > 1024:
+            if n <= comm.workspace().table.ll_units:
+                forced["ll_us"] = round(timed(
+                    lambda: ar.all_reduce_sum_(x, comm, algo=1), iters), 2)
+            if n * 4 * world <= half and n * 4 <= (16 << 20):
+                forced["oneshot_us"] = round(timed(
+                    lambda: ar.all_reduce_sum_(x, comm, algo=3), iters), 2)
+            if n * 4 >= (32 << 10) and comm.workspace().multicast():
+                forced["nvls_us"] = round(timed(
+                    lambda: ar.all_reduce_sum_(x, comm, algo=4), iters), 2)
+                if mc_x is not None and n <= mc_x.numel():
+                    xs = mc_x[:n]       # symmetric (multicast-resident) tensor
+                    xs.copy_(x)
+                    forced["nvls_inplace_us"] = round(timed(
+                        lambda: ar.all_reduce_sum_(xs, comm, algo=4), iters), 2)
+            if n * 4 <= half:
+                forced["twoshot_us"] = round(timed(
+                    lambda: ar.all_reduce_sum_(x, comm, algo=2), iters), 2)
         bytes_ = n * 4
         # bus bandwidth convention of nccl-tests: 2 (W-1)/W * bytes / time
         bus = lambda us: 2 * (world - 1) / world * bytes_ / (us * 1e-6) / 1e9
         row = {"bytes": bytes_, "n_gpus": world, "ours_us": round(ours, 2),
                "nccl_us": round(nccl, 2), "ours_busbw_gbs": round(bus(ours), 2),
                "nccl_busbw_gbs": round(bus(nccl), 2),
-               "algo": "LL" if n <= 4096 else "two-shot"}
+               **forced}
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)

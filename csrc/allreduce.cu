@@ -17,6 +17,12 @@ namespace {
 
 #define AR_LL_BLOCK 1024
 #define AR_BULK_BLOCK 512
+// auto policy: one-shot push up to MGB_ONESHOT_MAX_BYTES / W bytes (8 MiB at
+// 2 GPUs, 2 MiB at 8): measured crossover against the two-shot and NVLS
+// kernels (benchmarks/allreduce_sweep.py --all-algos, profiles/)
+#ifndef MGB_ONESHOT_MAX_BYTES
+#define MGB_ONESHOT_MAX_BYTES (16ull << 20)
+#endif
 
 // ---- LL all-reduce on a global array -------------------------------------
 template <typename T>
@@ -212,6 +218,122 @@ bulk_allreduce_f32_kernel(const MgbPeerTable pt, float* __restrict__ data,
   }
 }
 
+// ---- one-shot push all-reduce, float32 (mid-size messages) ------------------
+// Every rank stores its whole input into every peer's staging area
+// [parity][source rank][...] (bulk region A for even epochs, B for odd), so a
+// message crosses NVLink once and there is ONE synchronisation point: CTA c
+// of every rank handles the same element range and signals "my range is
+// staged" with an epoch-tagged flag in LL slot unit c; after the flags of all
+// peers arrived the CTA sums the W copies in rank order (bit-identical on
+// every rank).  No grid-wide barrier, no second exchange.  Two parities
+// suffice for the same reason as in the LL protocol: a peer can start the
+// next collective (and overwrite a staging area) only one exchange ahead,
+// and that one uses the other parity.  The last CTA to finish publishes the
+// epoch (every CTA has read it by then).
+__global__ void __launch_bounds__(AR_BULK_BLOCK, 1)
+oneshot_allreduce_f32_kernel(const MgbPeerTable pt, float* __restrict__ data,
+                             long long n4, long long tail_start, int ntail) {
+  __shared__ unsigned s_epoch;
+  const int tid = threadIdx.x;
+  const int W = pt.world, me = pt.rank;
+  unsigned* ctrl = mgb_ctrl(pt, me);
+  if (tid == 0) s_epoch = mgb_ld_sys_u32(ctrl + MGB_CTRL_EPOCH) + 1u;
+  __syncthreads();
+  const unsigned epoch = s_epoch, parity = epoch & 1u;
+  // upper half of region A / B: the two-shot kernel keeps the lower halves,
+  // so a rank that is still copying its two-shot result out of B cannot be
+  // overwritten by a peer that already started the next (one-shot) call
+  const unsigned long long off =
+      mgb_bulk_off(W, pt.ll_units) +
+      (parity ? ((pt.bulk_bytes + 1023ull) & ~1023ull) : 0ull) +
+      mgb_bulk_half(pt.bulk_bytes);
+  const long long n4t = n4 + (ntail ? 1 : 0);
+  const long long per = (n4t + gridDim.x - 1) / gridDim.x;
+  const long long lo = per * blockIdx.x;
+  const long long hi = min(lo + per, n4t);
+  float4* d4 = reinterpret_cast<float4*>(data);
+  // ---- push my range to every peer ----------------------------------------
+  for (long long i = lo + tid; i < hi; i += AR_BULK_BLOCK) {
+    float4 v;
+    if (i < n4) {
+      v = d4[i];
+    } else {
+      v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ntail > 0) v.x = data[tail_start];
+      if (ntail > 1) v.y = data[tail_start + 1];
+      if (ntail > 2) v.z = data[tail_start + 2];
+    }
+    for (int pi = 0; pi < W - 1; ++pi) {
+      int dst = me + 1 + pi;
+      if (dst >= W) dst -= W;
+      float4* slot = reinterpret_cast<float4*>((char*)pt.base[dst] + off) +
+                     (size_t)me * n4t + i;
+      st_peer_f4(slot, v);
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < W - 1) {
+    int dst = me + 1 + tid;
+    if (dst >= W) dst -= W;
+    mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, me, blockIdx.x),
+                   (unsigned long long)epoch << 32);
+  }
+  // ---- wait for the same range of every peer -------------------------------
+  if (tid < W && tid != me)
+    (void)mgb_ll_wait(pt, mgb_ll_slot(pt, me, parity, tid, blockIdx.x), epoch);
+  __syncthreads();
+  __threadfence_system();
+  // ---- ordered sum ----------------------------------------------------------
+  const float4* stage =
+      reinterpret_cast<const float4*>((const char*)pt.base[me] + off);
+  for (long long i = lo + tid; i < hi; i += AR_BULK_BLOCK) {
+    float4 mine;
+    if (i < n4) {
+      mine = d4[i];
+    } else {
+      mine = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ntail > 0) mine.x = data[tail_start];
+      if (ntail > 1) mine.y = data[tail_start + 1];
+      if (ntail > 2) mine.z = data[tail_start + 2];
+    }
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s0 = 0; s0 < W; s0 += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int s = s0 + k;
+        if (s < W)
+          v[k] = (s == me) ? mine : ld_peer_f4(stage + (size_t)s * n4t + i);
+        else
+          v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (s0 + k < W) {
+          acc.x += v[k].x; acc.y += v[k].y; acc.z += v[k].z; acc.w += v[k].w;
+        }
+    }
+    if (i < n4) {
+      d4[i] = acc;
+    } else {
+      if (ntail > 0) data[tail_start] = acc.x;
+      if (ntail > 1) data[tail_start + 1] = acc.y;
+      if (ntail > 2) data[tail_start + 2] = acc.z;
+    }
+  }
+  // ---- the last CTA publishes the epoch ------------------------------------
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned t = atomicAdd(ctrl + MGB_CTRL_TICKET, 1u);
+    if (t == gridDim.x - 1) {
+      ctrl[MGB_CTRL_TICKET] = 0u;
+      __threadfence();
+      mgb_st_sys_u32(ctrl + MGB_CTRL_EPOCH, epoch);
+    }
+  }
+}
+
 int g_bulk_grid[64] = {0};
 
 int bulk_grid() {
@@ -267,14 +389,39 @@ extern "C" int mgb_allreduce_sum(const MgbPeerTable* pt, void* data,
   MGB_REQUIRE(((uintptr_t)data & 15u) == 0, MGB_EINVAL,
               "mgb_allreduce_sum: data must be 16-byte aligned");
   const uint64_t need = ((n + 3ull) / 4ull) * 16ull;
-  MGB_REQUIRE(need <= pt->bulk_bytes, MGB_ETOOBIG,
-              "mgb_allreduce_sum: %llu bytes exceed the bulk region (%llu)",
-              (unsigned long long)need, (unsigned long long)pt->bulk_bytes);
+  const uint64_t half = mgb_bulk_half(pt->bulk_bytes);
+  MGB_REQUIRE(need <= half, MGB_ETOOBIG,
+              "mgb_allreduce_sum: %llu bytes exceed half the bulk region "
+              "(%llu)", (unsigned long long)need, (unsigned long long)half);
   MgbPeerTable ptv = *pt;
   float* d = (float*)data;
   long long n4 = (long long)(n / 4ull);
   long long tail_start = n4 * 4;
   int ntail = (int)(n - (uint64_t)tail_start);
+  // One-shot push: every rank receives W-1 copies, so it pays off while the
+  // message is small against the NVLink bandwidth (W-1)*n/BW, and it needs
+  // W staging copies in one bulk region and one flag unit per CTA.
+  const uint64_t oneshot_limit = MGB_ONESHOT_MAX_BYTES / (uint64_t)pt->world;
+  const bool fits_oneshot =
+      need * (uint64_t)pt->world <= pt->bulk_bytes - half;
+  bool oneshot = algo == 3 || (algo == 0 && need <= oneshot_limit);
+  if (algo == 3)
+    MGB_REQUIRE(fits_oneshot, MGB_ETOOBIG,
+                "mgb_allreduce_sum: one-shot staging needs %llu bytes, the "
+                "bulk region has %llu",
+                (unsigned long long)(need * pt->world),
+                (unsigned long long)(pt->bulk_bytes - half));
+  if (oneshot && fits_oneshot) {
+    const long long n4t = n4 + (ntail ? 1 : 0);
+    long long ctas = (n4t + 4 * AR_BULK_BLOCK - 1) / (4 * AR_BULK_BLOCK);
+    const long long cap = pt->ll_units < 128u ? pt->ll_units : 128u;
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    oneshot_allreduce_f32_kernel<<<(unsigned)ctas, AR_BULK_BLOCK, 0, st>>>(
+        ptv, d, n4, tail_start, ntail);
+    MGB_CUDA_CHECK(cudaGetLastError());
+    return MGB_OK;
+  }
   void* args[] = {&ptv, &d, &n4, &tail_start, &ntail};
   const int grid = bulk_grid();
   MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_allreduce_sum: no CUDA device");

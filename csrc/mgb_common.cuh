@@ -31,6 +31,7 @@ void mgb_set_error(const char* fmt, ...);
 #define MGB_CTRL_EPOCH 0      // uint32: last completed LL exchange epoch
 #define MGB_CTRL_ERROR 1      // uint32: sticky error flag (1 = spin timeout)
 #define MGB_CTRL_BULK_EPOCH 2 // uint32: last completed bulk collective
+#define MGB_CTRL_TICKET 3     // uint32: CTA completion ticket (one-shot push)
 
 __host__ __device__ inline unsigned long long mgb_ll_bytes(int world,
                                                           unsigned ll_units) {
@@ -40,6 +41,13 @@ __host__ __device__ inline unsigned long long mgb_bulk_off(int world,
                                                            unsigned ll_units) {
   unsigned long long o = MGB_CTRL_BYTES + mgb_ll_bytes(world, ll_units);
   return (o + 1023ull) & ~1023ull;
+}
+
+// Each bulk region is split in two: [0, half) belongs to the two-shot
+// all-reduce (and the K7 scatter windows), [half, bulk) to the one-shot push.
+__host__ __device__ inline unsigned long long mgb_bulk_half(
+    unsigned long long bulk_bytes) {
+  return (bulk_bytes / 2ull) & ~1023ull;
 }
 
 // -------------------------------------------------------------- device side

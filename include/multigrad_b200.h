@@ -72,10 +72,33 @@ int mgb_ws_read_ctrl(const void* local_base, int idx, uint32_t* out,
  * dtype: 0 = float32, 1 = float64.  In place on `data` (n elements).
  * Small messages use the one-shot ordered LL exchange (bit-identical result
  * on every rank); larger ones the two-shot reduce-scatter + all-gather over
- * peer loads/stores.  `algo`: 0 auto, 1 force LL, 2 force two-shot.
+ * peer loads/stores.  `algo`: 0 auto, 1 force LL, 2 force two-shot,
+ * 3 force one-shot push (mid-size float32 messages).
  * ---------------------------------------------------------------------- */
 int mgb_allreduce_sum(const MgbPeerTable* pt, void* data, uint64_t n,
                       int dtype, int algo, void* stream);
+/* ------------------------------------------------------------------------
+ * N1 (multicast) + K5 (NVLS): NVLink-switch multicast object of a
+ * communicator and the in-switch all-reduce (multimem.ld_reduce /
+ * multimem.st) on it.  Set-up order: root mgb_mc_create -> fd to the peers
+ * (unix socket) -> peers mgb_mc_import; all mgb_mc_add_device; barrier; all
+ * mgb_mc_bind; barrier.  No counterpart in the reference.
+ * ---------------------------------------------------------------------- */
+int mgb_mc_supported(int* out);
+int mgb_mc_round_size(int world, uint64_t bytes, uint64_t* out);
+int mgb_mc_create(int world, uint64_t bytes, uint64_t* handle_out, int* fd_out);
+int mgb_mc_import(int fd, uint64_t* handle_out);
+int mgb_mc_add_device(uint64_t handle);
+int mgb_mc_bind(uint64_t handle, uint64_t bytes, void** uc_out, void** mc_out,
+                uint64_t* mem_out);
+int mgb_mc_release(uint64_t handle, uint64_t mem, void* uc, void* mc,
+                   uint64_t bytes);
+/* float32 sum in place on `data`; `uc`/`mc` are this rank's unicast and the
+ * multicast view of the bound buffer (mc_bytes each); pt supplies the flags */
+int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc, void* mc,
+                           uint64_t mc_bytes, float* data, uint64_t n,
+                           void* stream);
+
 /* push `n` floats from `root` to every rank (K6, BFGS parameter hand-off;
  * replaces the pickled "compute"/params bcast of multigrad/bfgs.py:72-77).
  * Non-root ranks wait on the GPU until the data arrives. */

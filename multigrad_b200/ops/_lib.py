@@ -30,7 +30,7 @@ BUILD_DIR = ROOT / "build" / "obj"
 HASH_PATH = LIB_DIR / "libmgb200.hash"
 
 SOURCES = ["workspace.cu", "erfbin.cu", "allreduce.cu", "adam.cu",
-           "linlink.cu", "group.cu"]
+           "linlink.cu", "group.cu", "nvls.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
@@ -219,6 +219,21 @@ def _declare(lib: C.CDLL) -> None:
         lib.mgb_linlink_selftest.argtypes = [vp, vp, vp, vp, vp, vp, C.c_int,
                                              vp]
         lib.mgb_linlink_selftest.restype = C.c_int
+    lib.mgb_mc_supported.argtypes = [C.POINTER(C.c_int)]
+    lib.mgb_mc_round_size.argtypes = [C.c_int, u64, C.POINTER(u64)]
+    lib.mgb_mc_create.argtypes = [C.c_int, u64, C.POINTER(u64),
+                                  C.POINTER(C.c_int)]
+    lib.mgb_mc_import.argtypes = [C.c_int, C.POINTER(u64)]
+    lib.mgb_mc_add_device.argtypes = [u64]
+    lib.mgb_mc_bind.argtypes = [u64, u64, C.POINTER(vp), C.POINTER(vp),
+                                C.POINTER(u64)]
+    lib.mgb_mc_release.argtypes = [u64, u64, vp, vp, u64]
+    lib.mgb_allreduce_sum_nvls.argtypes = [C.POINTER(MgbPeerTable), vp, vp,
+                                           u64, vp, u64, vp]
+    for name in ("mgb_mc_supported", "mgb_mc_round_size", "mgb_mc_create",
+                 "mgb_mc_import", "mgb_mc_add_device", "mgb_mc_bind",
+                 "mgb_mc_release", "mgb_allreduce_sum_nvls"):
+        getattr(lib, name).restype = C.c_int
     lib.mgb_group_step.argtypes = [C.POINTER(MgbGroupArgs),
                                    C.POINTER(MgbStepArgs),
                                    C.POINTER(MgbPeerTable), vp]

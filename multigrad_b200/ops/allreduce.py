@@ -7,6 +7,7 @@ tensors: our own kernel, no NCCL/MPI (reference: host-staged MPI Allreduce,
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -15,6 +16,14 @@ from . import _lib
 __all__ = ["all_reduce_sum", "all_reduce_sum_", "bcast_", "launch_count"]
 
 _LAUNCHES = 0
+# auto policy: messages from this size on go through the NVLink-switch
+# reduction when the communicator has a multicast buffer (measured crossover,
+# benchmarks/allreduce_sweep.py --all-algos)
+NVLS_MIN_BYTES = int(os.environ.get("MULTIGRAD_B200_NVLS_MIN_BYTES", 2 << 20))
+NVLS_MIN_WORLD = 4      # with 2 GPUs the peer-store kernels win at every size
+# tensors allocated with PeerWorkspace.multicast_tensor() need no staging
+NVLS_INPLACE_MIN_BYTES = int(os.environ.get(
+    "MULTIGRAD_B200_NVLS_INPLACE_MIN_BYTES", 32 << 10))
 
 
 def launch_count() -> int:
@@ -28,8 +37,10 @@ def _stream():
 def all_reduce_sum_(t: torch.Tensor, comm, algo: int = 0) -> torch.Tensor:
     """In-place sum of a contiguous CUDA float32/float64 tensor over ``comm``.
 
-    ``algo``: 0 auto, 1 one-shot LL (ordered, bit-identical on every rank),
-    2 two-shot reduce-scatter/all-gather over peer loads and stores.
+    ``algo``: 0 auto, 3 one-shot push (mid-size float32),
+    1 one-shot LL (ordered, bit-identical on every rank),
+    2 two-shot reduce-scatter/all-gather over peer loads and stores,
+    4 in-switch reduction through an NVLink multicast object (NVLS).
     """
     global _LAUNCHES
     if comm is None or comm.size == 1 or t.numel() == 0:
@@ -56,9 +67,37 @@ def all_reduce_sum_(t: torch.Tensor, comm, algo: int = 0) -> torch.Tensor:
                     _stream()), "mgb_allreduce_sum")
                 _LAUNCHES += 1
             return t
-        if dt == 0 and algo != 1 and n * 4 > ws.table.bulk_bytes:
+        # large float32 messages: reduce inside the NVLink switch when the
+        # communicator has a multicast buffer (collective lazy set-up)
+        resident = (dt == 0 and ws._mc and (algo == 4 or (
+                    algo == 0 and comm.size >= NVLS_MIN_WORLD)) and
+                    ws._mc.uc <= t.data_ptr() < ws._mc.uc + ws._mc.bytes and
+                    n * 4 >= NVLS_INPLACE_MIN_BYTES)
+        if resident or (dt == 0 and (algo == 4 or (
+                algo == 0 and n * 4 >= NVLS_MIN_BYTES
+                and comm.size >= NVLS_MIN_WORLD))):
+            mc = ws.multicast()
+            if mc is None and algo == 4:
+                raise RuntimeError("all_reduce_sum: NVLS multicast is not "
+                                   "available on this communicator")
+            if mc is not None:
+                flat = t.view(-1)
+                # a tensor that lives in the bound buffer is reduced in place
+                # by the kernel (no staging), otherwise staged in chunks
+                step = n if resident else mc.bytes // 4
+                for lo in range(0, n, step):
+                    c = flat[lo:lo + step]
+                    _lib.check(lib.mgb_allreduce_sum_nvls(
+                        C.byref(ws.table), mc.uc, mc.mc, mc.bytes,
+                        c.data_ptr(), c.numel(), _stream()),
+                        "mgb_allreduce_sum_nvls")
+                    _LAUNCHES += 1
+                return t
+        # the bandwidth kernels own the lower half of each bulk region
+        half = (int(ws.table.bulk_bytes) // 2) & ~1023
+        if dt == 0 and algo != 1 and n * 4 > half:
             flat = t.view(-1)
-            step = int(ws.table.bulk_bytes // 4)
+            step = half // 4
             for lo in range(0, n, step):
                 c = flat[lo:lo + step]
                 _lib.check(lib.mgb_allreduce_sum(

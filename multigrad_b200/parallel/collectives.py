@@ -206,7 +206,7 @@ def _scatter_nd_device(array, axis, comm: Comm, root: int) -> torch.Tensor:
     dev = torch.device("cuda", torch.cuda.current_device())
     out = torch.empty((hi - lo,) + tuple(shape[1:]), dtype=dtype, device=dev)
     my_lo, my_hi = lo * row_bytes, hi * row_bytes
-    window = int(ws.table.bulk_bytes)
+    window = (int(ws.table.bulk_bytes) // 2) & ~1023   # lower half of A
     off = int(lib.mgb_ws_bulk_offset(comm.size, ws.table.ll_units))
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     total = rows * row_bytes

@@ -29,6 +29,15 @@ DEFAULT_BULK_BYTES = 64 << 20      # each of the two bulk regions
 DEFAULT_TIMEOUT_MS = 20000
 
 
+class _Multicast:
+    """Handles and the two views of a multicast-bound buffer."""
+    __slots__ = ("handle", "mem", "uc", "mc", "bytes")
+
+    def __init__(self, handle, mem, uc, mc, nbytes):
+        self.handle, self.mem = handle, mem
+        self.uc, self.mc, self.bytes = uc, mc, nbytes
+
+
 class PeerWorkspace:
     """Symmetric peer-mapped memory + the ``MgbPeerTable`` kernels consume."""
 
@@ -78,6 +87,117 @@ class PeerWorkspace:
             table.base[0] = local.value
         self.table = table
         self._closed = False
+        self._mc = False            # not set up yet (None = unavailable)
+        self._mc_used = 0           # bump allocator of multicast_tensor()
+
+    # -------------------------------------------------------------- multicast
+    def multicast(self):
+        """NVLink-switch multicast buffer of this communicator (built on first
+        use; collective call).  ``None`` when the GPUs / driver / topology do
+        not offer multicast objects, when the ranks are not on one host, or
+        with ``MULTIGRAD_B200_NVLS=0``: callers then fall back to the
+        peer-load kernels."""
+        if self._mc is False:
+            self._mc = self._setup_multicast()
+        return self._mc
+
+    def multicast_tensor(self, numel: int, dtype=torch.float32):
+        """A zeroed CUDA tensor carved out of the multicast-bound buffer
+        (symmetric memory: every rank must make the same sequence of calls so
+        that the tensors sit at the same offsets).  ``reduce_sum`` /
+        ``all_reduce_sum_`` on such a tensor runs entirely inside the NVLink
+        switch, without staging copies.  ``None`` when multicast is
+        unavailable or the buffer is exhausted."""
+        mc = self.multicast()
+        if mc is None:
+            return None
+        esz = torch.empty(0, dtype=dtype).element_size()
+        nbytes = (numel * esz + 255) & ~255
+        if self._mc_used + nbytes > mc.bytes:
+            return None
+        ptr = mc.uc + self._mc_used
+        self._mc_used += nbytes
+        typestr = {torch.float32: "<f4", torch.float64: "<f8",
+                   torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+
+        class _Raw:
+            __cuda_array_interface__ = {
+                "shape": (numel,), "typestr": typestr, "data": (ptr, False),
+                "version": 2}
+        t = torch.as_tensor(_Raw(), device=self.device)
+        t.zero_()
+        return t
+
+    def _setup_multicast(self):
+        import socket
+        lib, comm, world = self.lib, self.comm, self.comm.size
+        if world < 2:
+            return None
+        sup = C.c_int(0)
+        ok = (os.environ.get("MULTIGRAD_B200_NVLS", "1") != "0"
+              and lib.mgb_mc_supported(C.byref(sup)) == 0 and sup.value == 1
+              and hasattr(socket, "send_fds"))
+        votes = comm.allgather((bool(ok), socket.gethostname()))
+        if not all(v for v, _ in votes) or len({h for _, h in votes}) != 1:
+            return None
+        want = int(os.environ.get("MULTIGRAD_B200_MC_BYTES", 64 << 20))
+        size = C.c_uint64(0)
+        rc = lib.mgb_mc_round_size(world, want, C.byref(size))
+        if not all(r == 0 for r in comm.allgather(rc)):
+            return None
+        nbytes = int(size.value)
+        handle = C.c_uint64(0)
+        # the root creates the object and hands its file descriptor to every
+        # peer over an abstract unix socket (SCM_RIGHTS)
+        rc = 0
+        if comm.rank == 0:
+            fd = C.c_int(-1)
+            rc = lib.mgb_mc_create(world, nbytes, C.byref(handle),
+                                   C.byref(fd))
+            srv, name = None, None
+            if rc == 0:
+                name = "\0mgb-mc-%d-%x" % (os.getpid(), id(self))
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(name)
+                srv.listen(world)
+            comm.bcast(name, root=0)
+            if rc == 0:
+                srv.settimeout(60)
+                try:
+                    for _ in range(world - 1):
+                        conn, _a = srv.accept()
+                        socket.send_fds(conn, [b"fd"], [fd.value])
+                        conn.close()
+                except OSError:
+                    rc = -1
+                srv.close()
+                os.close(fd.value)
+        else:
+            name = comm.bcast(None, root=0)
+            if name is None:
+                rc = -1
+            else:
+                try:
+                    c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                    c.settimeout(60)
+                    c.connect(name)
+                    _msg, fds, _f, _a = socket.recv_fds(c, 16, 1)
+                    c.close()
+                    rc = lib.mgb_mc_import(fds[0], C.byref(handle))
+                    os.close(fds[0])
+                except (OSError, IndexError):
+                    rc = -1
+        if not all(r == 0 for r in comm.allgather(rc)):
+            return None
+        rc = lib.mgb_mc_add_device(handle.value)
+        if not all(r == 0 for r in comm.allgather(rc)):
+            return None             # (allgather doubles as the barrier)
+        uc, mc, mem = C.c_void_p(), C.c_void_p(), C.c_uint64(0)
+        rc = lib.mgb_mc_bind(handle.value, nbytes, C.byref(uc), C.byref(mc),
+                             C.byref(mem))
+        if not all(r == 0 for r in comm.allgather(rc)):
+            return None
+        return _Multicast(handle.value, mem.value, uc.value, mc.value, nbytes)
 
     # ------------------------------------------------------------------ state
     def read_ctrl(self, idx: int) -> int:
@@ -108,6 +228,10 @@ class PeerWorkspace:
             torch.cuda.synchronize()
             if self.comm.size > 1:
                 self.comm.Barrier()
+            if self._mc:
+                m = self._mc
+                self.lib.mgb_mc_release(m.handle, m.mem, m.uc, m.mc, m.bytes)
+                self._mc = None
             for p in self._imported:
                 self.lib.mgb_ws_unimport(p)
             self.lib.mgb_ws_free(self._local)

@@ -261,6 +261,9 @@ def gpu_allreduce_kernels():
                            (4096, torch.float32, 2), (5003, torch.float32, 0),
                            (100_001, torch.float32, 2),
                            ((1 << 20) + 3, torch.float32, 0),
+                           (4097, torch.float32, 3), (70_001, torch.float32, 3),
+                           (300_000, torch.float32, 3),
+                           (20_000, torch.float32, 0),
                            (6000, torch.float64, 0)]:
         full = torch.randn(SIZE, n, generator=g, dtype=torch.float64)
         mine = full[RANK].to(dtype).to(DEV)
@@ -274,6 +277,47 @@ def gpu_allreduce_kernels():
             blobs = COMM.allgather(out.cpu().numpy().tobytes())
             assert all(b == blobs[0] for b in blobs), (n, dtype, algo)
         assert torch.equal(mine.cpu(), full[RANK].to(dtype))   # input intact
+    # back-to-back calls of different algorithms share the workspace
+    full = torch.randn(SIZE, 50_000, generator=g, dtype=torch.float64)
+    want = full.float().double().sum(0)
+    for rep in range(4):
+        for algo in (3, 2, 3, 3, 1 if 50_000 <= COMM.workspace().table.ll_units
+                     else 3, 2, 3):
+            out = ar.all_reduce_sum(full[RANK].float().to(DEV), COMM, algo=algo)
+            err = (out.double().cpu() - want).abs().max() / want.abs().max()
+            assert err < 1e-6 * SIZE, (algo, rep, float(err))
+    # in-switch reduction (NVLS) where the box offers multicast objects
+    if COMM.workspace().multicast() is not None:
+        for n in (5, 4096, 100_003, (1 << 22) + 1):
+            full = torch.randn(SIZE, n, generator=g, dtype=torch.float64)
+            want = full.float().double().sum(0)
+            for rep in range(3):
+                out = ar.all_reduce_sum(full[RANK].float().to(DEV), COMM,
+                                        algo=4)
+                err = (out.double().cpu() - want).abs().max() / \
+                    want.abs().max()
+                assert err < 1e-6 * SIZE, ("nvls", n, rep, float(err))
+                blobs = COMM.allgather(out.cpu().numpy().tobytes())
+                assert all(b == blobs[0] for b in blobs), ("nvls", n)
+        out = ar.all_reduce_sum(full[RANK].float().to(DEV), COMM, algo=3 if
+                                full.shape[1] * 4 * SIZE <= (16 << 20) else 2)
+        assert (out.double().cpu() - want).abs().max() / want.abs().max() \
+            < 1e-6 * SIZE
+        # symmetric tensors (allocated in the multicast buffer): in place,
+        # ragged length, neighbours untouched
+        ws = COMM.workspace()
+        a = ws.multicast_tensor(70_003)
+        b = ws.multicast_tensor(1000)
+        b.fill_(7.0)
+        fa = torch.randn(SIZE, 70_003, generator=g, dtype=torch.float64)
+        for rep in range(3):
+            a.copy_(fa[RANK].float())
+            ar.all_reduce_sum_(a, COMM)
+            want = fa.float().double().sum(0)
+            err = (a.double().cpu() - want).abs().max() / want.abs().max()
+            assert err < 1e-6 * SIZE, ("nvls inplace", rep, float(err))
+            assert bool((b == 7.0).all())
+        print(f"[rank {RANK}] NVLS all-reduce checked", flush=True)
     # integer tensors go through float64
     t = mg.reduce_sum(torch.arange(5, device=DEV) * (RANK + 1))
     assert t.dtype == torch.int64

@@ -27,7 +27,7 @@ def build():
     LIB.parent.mkdir(parents=True, exist_ok=True)
     srcs = [str(ROOT / "csrc" / f) for f in
             ("workspace.cu", "erfbin.cu", "allreduce.cu", "adam.cu",
-             "linlink.cu", "group.cu")]
+             "linlink.cu", "group.cu", "nvls.cu")]
     subprocess.run(
         ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-DLL_TRACE", "-I",
