@@ -26,6 +26,7 @@
 // (multigrad/util.py:100-114).
 #include <math.h>
 #include <string.h>
+#include <time.h>
 #include <mutex>
 #include "mgb_common.cuh"
 #include "mgb_opt.cuh"
@@ -329,8 +330,13 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   // ---- parameters -> scaled link constants --------------------------------
   const float* pv =
       (a.mode >= MGB_MODE_ADAM) ? a.opt_p : (a.params + (size_t)b * md.nparams);
-  const float p_mu = pv[md.mu_idx];
-  const float p_sg = pv[md.sig_idx];
+  // one coalesced read per CTA: the vector may live in pinned host memory
+  // (zero-copy evaluation), where every separate request is a PCIe round trip
+  __shared__ float s_pv[MGB_MAX_PARAMS];
+  if (tid < md.nparams) s_pv[tid] = pv[tid];
+  __syncthreads();
+  const float p_mu = s_pv[md.mu_idx];
+  const float p_sg = s_pv[md.sig_idx];
   const double sigma_d =
       md.sigma_link == 1 ? exp10((double)p_sg) : (double)p_sg;
   // Scaled, *centred* coordinates: with xc = x - x0 (exact in fp32 for data
@@ -782,5 +788,111 @@ extern "C" int mgb_erfbin_eval_host(const MgbErfBinModel* model,
   MGB_CUDA_CHECK(cudaMemcpyAsync(out_host, d_out, sizeof(float) * (1 + P),
                                  cudaMemcpyDeviceToHost, st));
   MGB_CUDA_CHECK(cudaStreamSynchronize(st));
+  return MGB_OK;
+}
+
+// Zero-copy flavour of the above: the kernel reads the parameters straight
+// from the caller's pinned host buffer and writes (loss, grad) straight into
+// the pinned result buffer (both are device-accessible under unified
+// addressing), so one evaluation is ONE launch and no copy-engine operation;
+// the host waits by polling the result words, which it primed with a NaN
+// pattern no computation produces, instead of paying a stream synchronise.
+// Per evaluation P*4 bytes cross PCIe host->device and (1+P)*4 device->host.
+extern "C" int mgb_erfbin_eval_host_zc(const MgbErfBinModel* model,
+                                       const MgbPeerTable* pt,
+                                       const float* params_host,
+                                       float* out_host, void* scratch,
+                                       uint64_t scratch_bytes, void* stream,
+                                       uint32_t timeout_ms) {
+  MGB_REQUIRE(model && params_host && out_host, MGB_EINVAL,
+              "mgb_erfbin_eval_host_zc: null argument");
+  const int P = model->nparams;
+  MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
+              "mgb_erfbin_eval_host_zc: nparams=%d outside [1,%d]", P,
+              MGB_MAX_PARAMS);
+  const uint32_t kSentinel = 0x7fc0deadu;
+  volatile uint32_t* o = reinterpret_cast<volatile uint32_t*>(out_host);
+  for (int i = 0; i <= P; ++i) o[i] = kSentinel;
+  __sync_synchronize();
+  MgbStepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mode = MGB_MODE_LOSS_GRAD;
+  a.batch = 1;
+  a.reduce = (pt && pt->world > 1) ? 1 : 0;
+  a.params = params_host;
+  a.out_loss = out_host;
+  a.out_grad = out_host + 1;
+  const int rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
+  if (rc != MGB_OK) return rc;
+  struct timespec t0;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (unsigned spin = 0;; ++spin) {
+    bool done = true;
+    for (int i = 0; i <= P; ++i) done = done && (o[i] != kSentinel);
+    if (done) break;
+    if ((spin & 0x3ffu) == 0x3ffu) {
+      struct timespec t1;
+      clock_gettime(CLOCK_MONOTONIC, &t1);
+      const double ms = (t1.tv_sec - t0.tv_sec) * 1e3 +
+                        (t1.tv_nsec - t0.tv_nsec) * 1e-6;
+      if (ms > (double)timeout_ms) {
+        // distinguish "kernel failed" from "kernel slow"
+        const cudaError_t e = cudaStreamQuery((cudaStream_t)stream);
+        if (e != cudaSuccess && e != cudaErrorNotReady) MGB_CUDA_CHECK(e);
+        mgb_set_error("mgb_erfbin_eval_host_zc: no result after %u ms",
+                      timeout_ms);
+        return MGB_ESTATE;
+      }
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  __sync_synchronize();
+  return MGB_OK;
+}
+
+// Host-driven Adam in one native call: the optimiser state lives on the HOST
+// (as in the reference, where rank 0 owns it: multigrad/adam.py:52-68) and
+// every step ships the parameters to the GPU and the loss + gradient back
+// (zero-copy evaluation above), but without a Python round trip per step.
+// Every rank runs the same loop on bit-identical gradients, so the replicas
+// stay identical.  params_host / out_host must be pinned; m, v, traj,
+// loss_hist are ordinary host arrays (traj: (nsteps+1) x P with row 0 = the
+// initial parameters, loss_hist: nsteps; either may be NULL).
+extern "C" int mgb_erfbin_adam_host(
+    const MgbErfBinModel* model, const MgbPeerTable* pt, float* params_host,
+    float* out_host, float* m, float* v, int32_t step0, int32_t nsteps,
+    float lr, float b1, float b2, float eps, float* traj, float* loss_hist,
+    void* scratch, uint64_t scratch_bytes, void* stream,
+    uint32_t timeout_ms) {
+  MGB_REQUIRE(model && params_host && out_host && m && v && nsteps >= 0,
+              MGB_EINVAL, "mgb_erfbin_adam_host: bad arguments");
+  const int P = model->nparams;
+  MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
+              "mgb_erfbin_adam_host: nparams=%d outside [1,%d]", P,
+              MGB_MAX_PARAMS);
+  if (traj)
+    for (int i = 0; i < P; ++i) traj[i] = params_host[i];
+  for (int k = 0; k < nsteps; ++k) {
+    const int rc = mgb_erfbin_eval_host_zc(model, pt, params_host, out_host,
+                                           scratch, scratch_bytes, stream,
+                                           timeout_ms);
+    if (rc != MGB_OK) return rc;
+    const int step = step0 + k;
+    const float c1 = 1.0f - powf(b1, (float)(step + 1));
+    const float c2 = 1.0f - powf(b2, (float)(step + 1));
+    if (loss_hist) loss_hist[k] = out_host[0];
+    for (int i = 0; i < P; ++i) {
+      const float g = out_host[1 + i];
+      const float mi = (1.0f - b1) * g + b1 * m[i];
+      const float vi = (1.0f - b2) * g * g + b2 * v[i];
+      m[i] = mi;
+      v[i] = vi;
+      const float pn = params_host[i] - lr * (mi / c1) / (sqrtf(vi / c2) + eps);
+      params_host[i] = pn;
+      if (traj) traj[(size_t)(k + 1) * P + i] = pn;
+    }
+  }
   return MGB_OK;
 }

@@ -190,6 +190,25 @@ int mgb_erfbin_eval_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
                          const float* params_host, float* out_host,
                          float* d_params, float* d_out, void* scratch,
                          uint64_t scratch_bytes, void* stream);
+/* Zero-copy flavour: the kernel reads params_host and writes out_host (both
+ * pinned host memory) directly over PCIe, the host polls the result words:
+ * one launch, no copy-engine operation, no stream synchronise. */
+int mgb_erfbin_eval_host_zc(const MgbErfBinModel* model,
+                            const MgbPeerTable* pt, const float* params_host,
+                            float* out_host, void* scratch,
+                            uint64_t scratch_bytes, void* stream,
+                            uint32_t timeout_ms);
+/* Host-driven Adam (optimiser state on the host, as in the reference's
+ * multigrad/adam.py:52-68) without a Python round trip per step: nsteps x
+ * [zero-copy evaluation, Adam update in host memory].  params_host/out_host
+ * pinned; traj ((nsteps+1) x P, row 0 = start) and loss_hist may be NULL. */
+int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
+                         float* params_host, float* out_host, float* m,
+                         float* v, int32_t step0, int32_t nsteps, float lr,
+                         float b1, float b2, float eps, float* traj,
+                         float* loss_hist, void* scratch,
+                         uint64_t scratch_bytes, void* stream,
+                         uint32_t timeout_ms);
 
 /* Same fused step, for callers that cannot allocate scratch (a plug-in that
  * only receives its input/output buffers from a host runtime, a process whose

@@ -245,10 +245,14 @@ class ErfBinnedModel(OnePointModel):
     # --------------------------------------------------------- host fast path
     def loss_and_grad_host(self, params_host) -> "tuple[float, np.ndarray]":
         """Loss+gradient for host parameters with minimal host<->device
-        traffic, in ONE native call (``mgb_erfbin_eval_host``): pinned H2D
-        copy of ``P`` floats, the fused launch, pinned D2H copy of ``1+P``
-        floats, stream sync.  Used by ``run_bfgs`` and by the end-to-end
-        benchmark."""
+        traffic, in ONE native call.  Default (``mgb_erfbin_eval_host_zc``):
+        the fused kernel reads the ``P`` floats straight from a pinned host
+        buffer and writes its ``1+P`` result floats straight into another one
+        (zero copy over PCIe), the host polls for them: one launch, no
+        copy-engine operation, no stream synchronise.  With
+        ``MULTIGRAD_B200_ZEROCOPY=0`` (``mgb_erfbin_eval_host``): pinned H2D
+        copy, launch, pinned D2H copy, stream sync.  Used by ``run_bfgs`` and
+        by the end-to-end benchmark."""
         import ctypes as C
         plan = self.plan()
         if self._host is None:
@@ -259,26 +263,102 @@ class ErfBinnedModel(OnePointModel):
             d_out = torch.empty(1 + P, dtype=torch.float32,
                                 device=self.device)
             scratch = plan._scratch_for(1)
+            zc = os.environ.get("MULTIGRAD_B200_ZEROCOPY", "1") != "0"
+            if zc:
+                args = (C.byref(plan.model), plan._pt_ref,
+                        C.c_void_p(h_in.data_ptr()),
+                        C.c_void_p(h_out.data_ptr()),
+                        C.c_void_p(scratch.data_ptr()), scratch.numel())
+            else:
+                args = (C.byref(plan.model), plan._pt_ref,
+                        C.c_void_p(h_in.data_ptr()),
+                        C.c_void_p(h_out.data_ptr()),
+                        C.c_void_p(d_in.data_ptr()),
+                        C.c_void_p(d_out.data_ptr()),
+                        C.c_void_p(scratch.data_ptr()), scratch.numel())
             self._host = (h_in, h_out, d_in, d_out, scratch, h_in.numpy(),
-                          h_out.numpy(),
-                          (C.byref(plan.model), plan._pt_ref,
-                           C.c_void_p(h_in.data_ptr()),
-                           C.c_void_p(h_out.data_ptr()),
-                           C.c_void_p(d_in.data_ptr()),
-                           C.c_void_p(d_out.data_ptr()),
-                           C.c_void_p(scratch.data_ptr()), scratch.numel()))
+                          h_out.numpy(), args, zc)
         h = self._host
         h[5][:] = params_host
         if torch.cuda.current_device() != self.device.index:
             torch.cuda.set_device(self.device)
-        rc = plan.lib.mgb_erfbin_eval_host(
-            *h[7], C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        if h[8]:
+            timeout = 60000
+            if plan.pt is not None:
+                timeout = max(timeout, 2 * int(plan.pt.spin_timeout_ms))
+            rc = plan.lib.mgb_erfbin_eval_host_zc(*h[7], stream, timeout)
+        else:
+            rc = plan.lib.mgb_erfbin_eval_host(*h[7], stream)
         if rc:
             from ..ops import _lib
             _lib.check(rc, "mgb_erfbin_eval_host")
         from ..ops import erfbin as _eb
         _eb._LAUNCHES += 1
         return float(h[6][0]), h[6][1:].astype(np.float64)
+
+    def run_adam_host(self, guess, nsteps=100, learning_rate=0.01,
+                      init_state=None, return_state=False,
+                      return_loss=False):
+        """Adam with the optimiser state on the **host**, like the reference
+        (rank 0 owns it there, ``multigrad/adam.py:52-68``): every step writes
+        the parameters to pinned host memory, runs one fused launch that reads
+        them over PCIe and writes loss + gradient back into pinned host
+        memory, and applies the update on the CPU -- all inside ONE native
+        call (``mgb_erfbin_adam_host``), no Python per step.  Every rank runs
+        the same loop on bit-identical gradients.  Use :meth:`run_adam` when
+        nothing needs to see the per-step values on the host: it keeps the
+        whole fit on the device.  Unbounded parameters only.
+
+        Returns the trajectory ``(nsteps+1, ndim)`` as a CPU tensor (plus the
+        loss history / final :class:`AdamState` when asked for)."""
+        if not (self.fused and self._builtin_loss):
+            return super().run_adam(
+                guess, nsteps, None, learning_rate, init_state=init_state,
+                return_state=return_state, return_loss=return_loss)
+        import ctypes as C
+        plan = self.plan()
+        P = self.nparams
+        self.loss_and_grad_host(_np(guess).ravel())     # buffers + warm-up
+        h = self._host
+        h[5][:] = _np(guess).ravel()
+        step0 = 0
+        m = np.zeros(P, np.float32)
+        v = np.zeros(P, np.float32)
+        if init_state is not None:
+            step0 = int(init_state.step)
+            m[:] = _np(init_state.m)
+            v[:] = _np(init_state.v)
+        traj = np.zeros((nsteps + 1, P), np.float32)
+        losses = np.zeros(max(nsteps, 1), np.float32)
+        timeout = 60000
+        if plan.pt is not None:
+            timeout = max(timeout, 2 * int(plan.pt.spin_timeout_ms))
+        if torch.cuda.current_device() != self.device.index:
+            torch.cuda.set_device(self.device)
+        scratch = h[4]
+        rc = plan.lib.mgb_erfbin_adam_host(
+            C.byref(plan.model), plan._pt_ref, C.c_void_p(h[0].data_ptr()),
+            C.c_void_p(h[1].data_ptr()), m.ctypes.data_as(C.c_void_p),
+            v.ctypes.data_as(C.c_void_p), step0, int(nsteps),
+            float(learning_rate), _adam.ADAM_B1, _adam.ADAM_B2,
+            _adam.ADAM_EPS, traj.ctypes.data_as(C.c_void_p),
+            losses.ctypes.data_as(C.c_void_p),
+            C.c_void_p(scratch.data_ptr()), scratch.numel(),
+            C.c_void_p(torch.cuda.current_stream().cuda_stream), timeout)
+        if rc:
+            from ..ops import _lib
+            _lib.check(rc, "mgb_erfbin_adam_host")
+        from ..ops import erfbin as _eb
+        _eb._LAUNCHES += int(nsteps)
+        self._check_peers()
+        out = [torch.from_numpy(traj)]
+        if return_loss:
+            out.append(torch.from_numpy(losses[:nsteps]))
+        if return_state:
+            out.append(_adam.AdamState(step0 + nsteps, torch.from_numpy(m),
+                                       torch.from_numpy(v)))
+        return out[0] if len(out) == 1 else tuple(out)
 
     # ------------------------------------------------- device-resident driver
     def device_loss_grad_launcher(self, params: torch.Tensor,

@@ -211,6 +211,14 @@ def _declare(lib: C.CDLL) -> None:
                                          C.POINTER(MgbPeerTable), vp, vp, vp,
                                          vp, vp, u64, vp]
     lib.mgb_erfbin_eval_host.restype = C.c_int
+    lib.mgb_erfbin_eval_host_zc.argtypes = [C.POINTER(MgbErfBinModel),
+                                            C.POINTER(MgbPeerTable), vp, vp,
+                                            vp, u64, vp, u32]
+    lib.mgb_erfbin_eval_host_zc.restype = C.c_int
+    lib.mgb_erfbin_adam_host.argtypes = [
+        C.POINTER(MgbErfBinModel), C.POINTER(MgbPeerTable), vp, vp, vp, vp,
+        i32, i32, f32, f32, f32, f32, vp, vp, vp, u64, vp, u32]
+    lib.mgb_erfbin_adam_host.restype = C.c_int
     lib.mgb_erfbin_step_static.argtypes = [C.POINTER(MgbErfBinModel),
                                            C.POINTER(MgbStepArgs),
                                            C.POINTER(MgbPeerTable), vp]

@@ -352,6 +352,11 @@ def gpu_fused_step_uses_one_launch():
     ts = model.run_adam([-1.9, 0.3], nsteps=120, learning_rate=0.01,
                         use_graph=False)
     assert torch.equal(tg, ts)
+    # host-driven Adam (state on the host): same trajectory on every rank
+    th = model.run_adam_host([-1.9, 0.3], nsteps=25, learning_rate=0.01)
+    assert torch.allclose(th, ts[:26].cpu(), rtol=1e-5, atol=2e-6)
+    blobs = COMM.allgather(th.numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
 
 
 @case

@@ -290,6 +290,45 @@ def test_bfgs_tutorial_on_gpu():
     assert abs(l - 0.44032094) < 3e-5 and g.shape == (2,)
 
 
+def test_host_eval_zero_copy_equals_copy_path(monkeypatch):
+    """loss_and_grad_host: the zero-copy flavour (kernel reads/writes pinned
+    host memory, host polls) returns the same bits as the memcpy flavour."""
+    pts = [[-1.9, 0.3], [-2.2, 0.15], [-1.2, 0.6]]
+    out = {}
+    for zc in ("1", "0"):
+        monkeypatch.setenv("MULTIGRAD_B200_ZEROCOPY", zc)
+        m, *_ = make(n=50_000, k=10, seed=3)
+        m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+        out[zc] = [m.loss_and_grad_host(p) for p in pts for _ in range(3)]
+        assert m._host[8] == (zc == "1")
+    for (l1, g1), (l0, g0) in zip(out["1"], out["0"]):
+        assert l1 == l0 and np.array_equal(g1, g0)
+    ref_l, ref_g = m.calc_loss_and_grad_from_params(pts[-1])
+    assert abs(out["1"][-1][0] - float(ref_l)) < 1e-6 * max(1, abs(float(ref_l)))
+    assert np.allclose(out["1"][-1][1], ref_g.cpu().numpy(), rtol=1e-6)
+
+
+def test_run_adam_host_matches_device_adam():
+    """Host-driven Adam (state on the host, native loop) follows the same
+    trajectory as the device-resident fit, and resumes."""
+    m, *_ = make(n=40_000, k=10, seed=4)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    guess = [-1.7, 0.35]
+    th, lh, sh = m.run_adam_host(guess, nsteps=30, learning_rate=0.02,
+                                 return_loss=True, return_state=True)
+    td, ld = m.run_adam(guess, nsteps=30, learning_rate=0.02,
+                        return_loss=True)
+    assert th.shape == (31, 2) and not th.is_cuda
+    assert torch.allclose(th, td.cpu(), rtol=1e-5, atol=2e-6)
+    # (the two Adam implementations round differently: ~1e-6 in the
+    # parameters, amplified near the minimum of the loss)
+    assert torch.allclose(lh, ld.cpu(), rtol=5e-3, atol=1e-6)
+    assert sh.step == 30
+    t2 = m.run_adam_host(th[-1], nsteps=5, learning_rate=0.02, init_state=sh)
+    full = m.run_adam_host(guess, nsteps=35, learning_rate=0.02)
+    assert torch.allclose(t2[-1], full[-1], rtol=1e-6, atol=1e-7)
+
+
 def test_custom_loss_uses_sumstats_plus_jacobian_path():
     class Custom(ErfBinnedModel):
         def calc_loss_from_sumstats(self, sumstats, sumstats_aux=None,
