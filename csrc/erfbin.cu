@@ -25,6 +25,7 @@
 // (multigrad/adam.py:52-68), transforms (adam.py:192-239), simple_grad_descent
 // (multigrad/util.py:100-114).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <time.h>
 #include <mutex>
@@ -32,6 +33,13 @@
 #include "mgb_opt.cuh"
 
 #define EB_SENTINEL_X 1.0e30f // padding object: contributes exactly zero
+
+// word of the counter block used as host-hand-shake relay (batch == 1 only:
+// the block is 64 words, the ticket counter is word 0)
+#define EB_RELAY_WORD 32
+#ifndef EB_HOST_POLL_NS
+#define EB_HOST_POLL_NS 100
+#endif
 
 namespace {
 
@@ -327,14 +335,76 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   // gated launch: uniform early exit on every rank (no ticket, no exchange)
   if (a.gate != nullptr && __ldg(a.gate) == 0.0f) return;
 
-  // ---- parameters -> scaled link constants --------------------------------
-  const float* pv =
-      (a.mode >= MGB_MODE_ADAM) ? a.opt_p : (a.params + (size_t)b * md.nparams);
-  // one coalesced read per CTA: the vector may live in pinned host memory
-  // (zero-copy evaluation), where every separate request is a PCIe round trip
+  // pre-launched host-driven step: wait for the host to publish this step's
+  // parameters.  Only CTA 0 talks to the host: a system-scope load of pinned
+  // host memory is a PCIe round trip that is not merged with anybody else's
+  // (296 CTAs polling the same word cost ~270 us per step, measured), so
+  // CTA 0 polls the flag, fetches the parameters and relays both through
+  // device memory (spare words of the counter block), where the other CTAs
+  // wait at L2 latency.  Relay token = wait_value (go) or wait_value with
+  // bit 31 set (cancelled / timed out); the host zeroes it before a run.
   __shared__ float s_pv[MGB_MAX_PARAMS];
-  if (tid < md.nparams) s_pv[tid] = pv[tid];
-  __syncthreads();
+  if (a.wait_flag != nullptr) {
+    __shared__ unsigned s_tok;
+    unsigned* relay_tok = counters + EB_RELAY_WORD;
+    float* relay_pv = reinterpret_cast<float*>(counters + EB_RELAY_WORD + 8);
+    const unsigned long long t0 = mgb_globaltimer_ns();
+    const unsigned long long limit =
+        (unsigned long long)a.wait_timeout_ms * 1000000ull;
+    if (blockIdx.x == 0) {
+      if (tid == 0) {
+        unsigned tok = a.wait_value | 0x80000000u;
+        for (unsigned it = 0;; ++it) {
+          const unsigned f = mgb_ld_sys_u32(a.wait_flag);
+          if (f & 0x80000000u) break;                       // cancelled
+          if ((f & 0x7fffffffu) >= a.wait_value) { tok = a.wait_value; break; }
+          if ((it & 15u) == 15u && mgb_globaltimer_ns() - t0 > limit) break;
+          __nanosleep(EB_HOST_POLL_NS);
+        }
+        __threadfence_system();   // acquire: parameters written before flag
+        s_tok = tok;
+      }
+      __syncthreads();
+      if (!(s_tok & 0x80000000u) && tid < md.nparams) {
+        const float v = __uint_as_float(mgb_ld_sys_u32(
+            reinterpret_cast<const unsigned*>(a.params) + tid));
+        s_pv[tid] = v;
+        relay_pv[tid] = v;
+      }
+      __threadfence();
+      __syncthreads();
+      if (tid == 0)
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(relay_tok),
+                     "r"(s_tok) : "memory");
+    } else {
+      if (tid == 0) {
+        unsigned tok = a.wait_value | 0x80000000u;
+        for (unsigned it = 0;; ++it) {
+          unsigned f;
+          asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(f)
+                       : "l"(relay_tok) : "memory");
+          if ((f & 0x7fffffffu) == a.wait_value) { tok = f; break; }
+          if ((it & 63u) == 63u && mgb_globaltimer_ns() - t0 > 2 * limit) break;
+        }
+        __threadfence();
+        s_tok = tok;
+      }
+      __syncthreads();
+      if (!(s_tok & 0x80000000u) && tid < md.nparams)
+        s_pv[tid] = __ldcv(relay_pv + tid);
+    }
+    __syncthreads();
+    if (s_tok & 0x80000000u) return;
+  } else {
+    // ---- parameters: one coalesced read per CTA (the vector may live in
+    // pinned host memory: zero-copy evaluation) ------------------------------
+    const float* pv = (a.mode >= MGB_MODE_ADAM)
+                          ? a.opt_p
+                          : (a.params + (size_t)b * md.nparams);
+    if (tid < md.nparams) s_pv[tid] = pv[tid];
+    __syncthreads();
+  }
+  // ---- parameters -> scaled link constants --------------------------------
   const float p_mu = s_pv[md.mu_idx];
   const float p_sg = s_pv[md.sig_idx];
   const double sigma_d =
@@ -632,6 +702,11 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   const EbLayout lay = make_layout(md.nbins, &et_hi);
   const int grid = grid_for(md.nbins);
   MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_erfbin_step: no CUDA device");
+  MGB_REQUIRE(a.wait_flag == nullptr ||
+                  (a.batch == 1 && a.mode <= MGB_MODE_LOSS_GRAD),
+              MGB_EINVAL,
+              "mgb_erfbin_step: the host hand-shake needs batch == 1 and an "
+              "evaluation mode");
   const uint64_t need = mgb_erfbin_scratch_bytes(md.nbins, a.batch);
   MGB_REQUIRE(scratch_bytes >= need, MGB_ETOOBIG,
               "mgb_erfbin_step: scratch %llu < %llu bytes",
@@ -874,11 +949,75 @@ extern "C" int mgb_erfbin_adam_host(
               MGB_MAX_PARAMS);
   if (traj)
     for (int i = 0; i < P; ++i) traj[i] = params_host[i];
-  for (int k = 0; k < nsteps; ++k) {
-    const int rc = mgb_erfbin_eval_host_zc(model, pt, params_host, out_host,
-                                           scratch, scratch_bytes, stream,
-                                           timeout_ms);
+  if (nsteps == 0) return MGB_OK;
+  // Pipelining: the launch for step k+1 is issued while step k computes, and
+  // its grid waits (on the GPU, polling a word of out_host over PCIe) until
+  // the host has published the parameters of step k+1.  The launch latency
+  // therefore never sits between two steps.  Layout of out_host:
+  //   [0] loss, [1..P] gradient, [MGB_HOST_FLAG_WORD] (as uint32, in its own
+  //   cache line) the hand-shake word.
+  const uint32_t kSentinel = 0x7fc0deadu;
+  volatile uint32_t* o = reinterpret_cast<volatile uint32_t*>(out_host);
+  volatile uint32_t* flag = o + MGB_HOST_FLAG_WORD;
+  const char* env = getenv("MULTIGRAD_B200_HOST_PIPELINE");
+  const bool pipelined = !(env && env[0] == '0');
+  *flag = 0u;
+  MgbStepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mode = MGB_MODE_LOSS_GRAD;
+  a.batch = 1;
+  a.reduce = (pt && pt->world > 1) ? 1 : 0;
+  a.params = params_host;
+  a.out_loss = out_host;
+  a.out_grad = out_host + 1;
+  a.wait_flag = const_cast<const uint32_t*>(
+      reinterpret_cast<uint32_t*>(out_host) + MGB_HOST_FLAG_WORD);
+  a.wait_timeout_ms = timeout_ms;
+  int rc = MGB_OK;
+  // the device-side relay of the hand-shake starts from zero
+  MGB_REQUIRE(scratch != nullptr && scratch_bytes >= 256, MGB_EINVAL,
+              "mgb_erfbin_adam_host: scratch missing");
+  MGB_CUDA_CHECK(cudaMemsetAsync(
+      reinterpret_cast<char*>(scratch) + 4 * EB_RELAY_WORD, 0,
+      256 - 4 * EB_RELAY_WORD, (cudaStream_t)stream));
+  a.wait_value = 1u;
+  if (pipelined) {
+    rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
     if (rc != MGB_OK) return rc;
+  }
+  for (int k = 0; k < nsteps; ++k) {
+    // publish step k: results primed, parameters in place, then the flag
+    for (int i = 0; i <= P; ++i) o[i] = kSentinel;
+    __sync_synchronize();
+    *flag = (uint32_t)(k + 1);
+    // queue the next step's grid behind this one (it waits for flag k+2)
+    a.wait_value = (uint32_t)(pipelined ? k + 2 : k + 1);
+    rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
+    if (rc != MGB_OK) break;
+    struct timespec t0;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (unsigned spin = 0;; ++spin) {
+      bool done = true;
+      for (int i = 0; i <= P; ++i) done = done && (o[i] != kSentinel);
+      if (done) break;
+      if ((spin & 0x3ffu) == 0x3ffu) {
+        struct timespec t1;
+        clock_gettime(CLOCK_MONOTONIC, &t1);
+        const double ms = (t1.tv_sec - t0.tv_sec) * 1e3 +
+                          (t1.tv_nsec - t0.tv_nsec) * 1e-6;
+        if (ms > (double)timeout_ms) {
+          mgb_set_error("mgb_erfbin_adam_host: no result for step %d after "
+                        "%u ms", k, timeout_ms);
+          rc = MGB_ESTATE;
+          break;
+        }
+      }
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+    if (rc != MGB_OK) break;
+    __sync_synchronize();
     const int step = step0 + k;
     const float c1 = 1.0f - powf(b1, (float)(step + 1));
     const float c2 = 1.0f - powf(b2, (float)(step + 1));
@@ -894,5 +1033,10 @@ extern "C" int mgb_erfbin_adam_host(
       if (traj) traj[(size_t)(k + 1) * P + i] = pn;
     }
   }
-  return MGB_OK;
+  // release the one grid that is still waiting, and wait for it to leave
+  __sync_synchronize();
+  *flag = 0x80000000u;
+  const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  if (rc == MGB_OK && e != cudaSuccess) MGB_CUDA_CHECK(e);
+  return rc;
 }

@@ -172,6 +172,14 @@ typedef struct MgbStepArgs {
   int32_t bound_kind[MGB_MAX_PARAMS]; /* 0 none 1 both 2 low-only 3 high-only */
   float bound_lo[MGB_MAX_PARAMS];
   float bound_hi[MGB_MAX_PARAMS];
+  /* Host hand-shake (pre-launched host-driven steps, mgb_erfbin_adam_host):
+   * when non-NULL the grid starts working only once the low 31 bits of
+   * *wait_flag (pinned host memory, polled over PCIe) reach wait_value;
+   * bit 31 set = cancelled, the grid exits without touching anything; after
+   * wait_timeout_ms without either it exits as if cancelled. */
+  const uint32_t* wait_flag;
+  uint32_t wait_value;
+  uint32_t wait_timeout_ms;
 } MgbStepArgs;
 
 /* scratch needed by mgb_erfbin_step: bytes for `scratch` given the batch */
@@ -202,6 +210,7 @@ int mgb_erfbin_eval_host_zc(const MgbErfBinModel* model,
  * multigrad/adam.py:52-68) without a Python round trip per step: nsteps x
  * [zero-copy evaluation, Adam update in host memory].  params_host/out_host
  * pinned; traj ((nsteps+1) x P, row 0 = start) and loss_hist may be NULL. */
+#define MGB_HOST_FLAG_WORD 16  /* out_host needs MGB_HOST_FLAG_WORD + 1 words */
 int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
                          float* params_host, float* out_host, float* m,
                          float* v, int32_t step0, int32_t nsteps, float lr,

@@ -258,7 +258,9 @@ class ErfBinnedModel(OnePointModel):
         if self._host is None:
             P = self.nparams
             h_in = torch.empty(P, dtype=torch.float32).pin_memory()
-            h_out = torch.empty(1 + P, dtype=torch.float32).pin_memory()
+            # loss, gradient, + the hand-shake word of the pipelined host loop
+            # (word 16, in its own cache line: MGB_HOST_FLAG_WORD)
+            h_out = torch.zeros(32, dtype=torch.float32).pin_memory()
             d_in = torch.empty(P, dtype=torch.float32, device=self.device)
             d_out = torch.empty(1 + P, dtype=torch.float32,
                                 device=self.device)
@@ -295,7 +297,7 @@ class ErfBinnedModel(OnePointModel):
             _lib.check(rc, "mgb_erfbin_eval_host")
         from ..ops import erfbin as _eb
         _eb._LAUNCHES += 1
-        return float(h[6][0]), h[6][1:].astype(np.float64)
+        return float(h[6][0]), h[6][1:1 + self.nparams].astype(np.float64)
 
     def run_adam_host(self, guess, nsteps=100, learning_rate=0.01,
                       init_state=None, return_state=False,

@@ -83,6 +83,8 @@ class MgbStepArgs(C.Structure):
         ("bound_kind", C.c_int32 * MGB_MAX_PARAMS),
         ("bound_lo", C.c_float * MGB_MAX_PARAMS),
         ("bound_hi", C.c_float * MGB_MAX_PARAMS),
+        ("wait_flag", C.c_void_p), ("wait_value", C.c_uint32),
+        ("wait_timeout_ms", C.c_uint32),
     ]
 
 
