@@ -210,6 +210,17 @@ int mgb_erfbin_eval_host_zc(const MgbErfBinModel* model,
  * multigrad/adam.py:52-68) without a Python round trip per step: nsteps x
  * [zero-copy evaluation, Adam update in host memory].  params_host/out_host
  * pinned; traj ((nsteps+1) x P, row 0 = start) and loss_hist may be NULL. */
+/* Root side of one multi-GPU L-BFGS-B evaluation (K6) in one call: control
+ * block (gate, params; pinned host) -> device, LL broadcast to the workers,
+ * gated fused launch writing (loss, grad) into pinned out_host, poll.  With
+ * gate == 0 nothing is waited for (the exit blocks that drain the workers'
+ * queued launches).  Replaces the pickled broadcasts of
+ * multigrad/bfgs.py:72-77. */
+int mgb_erfbin_bfgs_root_eval(const MgbErfBinModel* model,
+                              const MgbPeerTable* pt, const float* ctl_host,
+                              float* ctl_dev, float* out_host, void* scratch,
+                              uint64_t scratch_bytes, void* stream,
+                              uint32_t timeout_ms);
 #define MGB_HOST_FLAG_WORD 16  /* out_host needs MGB_HOST_FLAG_WORD + 1 words */
 int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
                          float* params_host, float* out_host, float* m,

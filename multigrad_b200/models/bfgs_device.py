@@ -49,20 +49,33 @@ def run_bfgs_device(model, guess, maxsteps, param_bounds, comm):
     stream = torch.cuda.current_stream(dev)
 
     if comm.rank == 0:
+        import ctypes as C
         h_in = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
         h_out = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
+        n_in, n_out = h_in.numpy(), h_out.numpy()
+        scratch = plan._scratch_for(1)
+        timeout = max(60000, 2 * int(plan.pt.spin_timeout_ms))
+        if torch.cuda.current_device() != dev.index:
+            torch.cuda.set_device(dev)
+        call = (C.byref(plan.model), plan._pt_ref,
+                C.c_void_p(h_in.data_ptr()), C.c_void_p(ctl.data_ptr()),
+                C.c_void_p(h_out.data_ptr()), C.c_void_p(scratch.data_ptr()),
+                scratch.numel(), C.c_void_p(stream.cuda_stream), timeout)
         pbar = util.trange(maxsteps, desc="BFGS Gradient Descent Progress",
                            leave=True)
 
+        def root_eval():
+            # ONE native call: control block H2D, NVLink push to the workers,
+            # gated fused launch, results polled in pinned host memory
+            rc = plan.lib.mgb_erfbin_bfgs_root_eval(*call)
+            if rc:
+                _lib.check(rc, "mgb_erfbin_bfgs_root_eval")
+
         def fn(p):
-            h_in[0] = 1.0
-            h_in[1:] = torch.as_tensor(np.asarray(p, dtype=np.float32))
-            ctl.copy_(h_in, non_blocking=True)
-            bcast_(ctl, comm, root=0)
-            plan.launch(a)
-            h_out.copy_(d_out, non_blocking=True)
-            stream.synchronize()
-            return float(h_out[0]), h_out[1:].double().numpy().copy()
+            n_in[0] = 1.0
+            n_in[1:] = p
+            root_eval()
+            return float(n_out[0]), n_out[1:].astype(np.float64)
 
         def callback(*_a, **_k):
             if hasattr(pbar, "update"):
@@ -79,11 +92,9 @@ def run_bfgs_device(model, guess, maxsteps, param_bounds, comm):
         finally:
             if hasattr(pbar, "close"):
                 pbar.close()
-            h_in.zero_()
+            n_in[:] = 0.0
             for _ in range(DEPTH):
-                ctl.copy_(h_in, non_blocking=True)
-                bcast_(ctl, comm, root=0)
-                plan.launch(a)          # gated no-op, keeps launch parity
+                root_eval()             # gated no-op, keeps launch parity
             stream.synchronize()
         comm.bcast(("error", repr(err)) if err is not None else
                    ("ok", [*result.keys()], [*result.values()]), root=0)
