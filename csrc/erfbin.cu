@@ -940,9 +940,11 @@ extern "C" int mgb_erfbin_adam_host(
     float* out_host, float* m, float* v, int32_t step0, int32_t nsteps,
     float lr, float b1, float b2, float eps, float* traj, float* loss_hist,
     void* scratch, uint64_t scratch_bytes, void* stream,
-    uint32_t timeout_ms) {
+    uint32_t timeout_ms, void* flush_buf, uint64_t flush_bytes,
+    double* timed_seconds) {
   MGB_REQUIRE(model && params_host && out_host && m && v && nsteps >= 0,
               MGB_EINVAL, "mgb_erfbin_adam_host: bad arguments");
+  if (timed_seconds) *timed_seconds = 0.0;
   const int P = model->nparams;
   MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
               "mgb_erfbin_adam_host: nparams=%d outside [1,%d]", P,
@@ -980,22 +982,54 @@ extern "C" int mgb_erfbin_adam_host(
   MGB_CUDA_CHECK(cudaMemsetAsync(
       reinterpret_cast<char*>(scratch) + 4 * EB_RELAY_WORD, 0,
       256 - 4 * EB_RELAY_WORD, (cudaStream_t)stream));
+  // Benchmarking aid: with flush_buf the L2 is overwritten (a fill larger
+  // than the cache) in front of every step's grid, and the time the host
+  // waits for that fill is kept out of *timed_seconds, which then sums, per
+  // step, the interval [parameters published, loss+grad read back].
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  if (flush_buf) {
+    MGB_CUDA_CHECK(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    MGB_CUDA_CHECK(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+  }
+#define EB_FLUSH(idx)                                                         \
+  do {                                                                        \
+    if (flush_buf && rc == MGB_OK) {                                          \
+      cudaError_t e_ = cudaMemsetAsync(flush_buf, (idx) + 1, flush_bytes, st); \
+      if (e_ == cudaSuccess) e_ = cudaEventRecord(ev[(idx) & 1], st);         \
+      if (e_ != cudaSuccess) {                                                \
+        mgb_set_error("mgb_erfbin_adam_host: flush failed: %s",               \
+                      cudaGetErrorString(e_));                                \
+        rc = (int)e_;                                                         \
+      }                                                                       \
+    }                                                                         \
+  } while (0)
   a.wait_value = 1u;
   if (pipelined) {
-    rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
-    if (rc != MGB_OK) return rc;
+    EB_FLUSH(0);
+    if (rc == MGB_OK)
+      rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
   }
-  for (int k = 0; k < nsteps; ++k) {
+  double timed = 0.0;
+  for (int k = 0; k < nsteps && rc == MGB_OK; ++k) {
+    if (!pipelined) EB_FLUSH(k);
+    if (flush_buf && rc == MGB_OK) {
+      const cudaError_t e_ = cudaEventSynchronize(ev[k & 1]);
+      if (e_ != cudaSuccess) { rc = (int)e_; break; }
+    }
+    if (rc != MGB_OK) break;
+    struct timespec t0;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
     // publish step k: results primed, parameters in place, then the flag
     for (int i = 0; i <= P; ++i) o[i] = kSentinel;
     __sync_synchronize();
     *flag = (uint32_t)(k + 1);
     // queue the next step's grid behind this one (it waits for flag k+2)
     a.wait_value = (uint32_t)(pipelined ? k + 2 : k + 1);
+    if (pipelined) EB_FLUSH(k + 1);
+    if (rc != MGB_OK) break;
     rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
     if (rc != MGB_OK) break;
-    struct timespec t0;
-    clock_gettime(CLOCK_MONOTONIC, &t0);
     for (unsigned spin = 0;; ++spin) {
       bool done = true;
       for (int i = 0; i <= P; ++i) done = done && (o[i] != kSentinel);
@@ -1032,11 +1066,18 @@ extern "C" int mgb_erfbin_adam_host(
       params_host[i] = pn;
       if (traj) traj[(size_t)(k + 1) * P + i] = pn;
     }
+    struct timespec t2;
+    clock_gettime(CLOCK_MONOTONIC, &t2);
+    timed += (t2.tv_sec - t0.tv_sec) + (t2.tv_nsec - t0.tv_nsec) * 1e-9;
   }
+#undef EB_FLUSH
+  if (timed_seconds) *timed_seconds = timed;
   // release the one grid that is still waiting, and wait for it to leave
   __sync_synchronize();
   *flag = 0x80000000u;
   const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  if (ev[0]) cudaEventDestroy(ev[0]);
+  if (ev[1]) cudaEventDestroy(ev[1]);
   if (rc == MGB_OK && e != cudaSuccess) MGB_CUDA_CHECK(e);
   return rc;
 }

@@ -228,7 +228,12 @@ int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
                          float b1, float b2, float eps, float* traj,
                          float* loss_hist, void* scratch,
                          uint64_t scratch_bytes, void* stream,
-                         uint32_t timeout_ms);
+                         uint32_t timeout_ms, void* flush_buf,
+                         uint64_t flush_bytes, double* timed_seconds);
+/* flush_buf (optional, benchmarking): device buffer larger than L2 that is
+ * overwritten in front of every step; *timed_seconds (optional) receives the
+ * sum over steps of [params published -> loss+grad read back], which leaves
+ * the wait for that fill out. */
 
 /* Same fused step, for callers that cannot allocate scratch (a plug-in that
  * only receives its input/output buffers from a host runtime, a process whose

@@ -301,7 +301,7 @@ class ErfBinnedModel(OnePointModel):
 
     def run_adam_host(self, guess, nsteps=100, learning_rate=0.01,
                       init_state=None, return_state=False,
-                      return_loss=False):
+                      return_loss=False, _flush_l2=None):
         """Adam with the optimiser state on the **host**, like the reference
         (rank 0 owns it there, ``multigrad/adam.py:52-68``): every step writes
         the parameters to pinned host memory, runs one fused launch that reads
@@ -339,6 +339,13 @@ class ErfBinnedModel(OnePointModel):
         if torch.cuda.current_device() != self.device.index:
             torch.cuda.set_device(self.device)
         scratch = h[4]
+        # benchmarking aid: a CUDA uint8 tensor larger than L2 that is
+        # overwritten in front of every step; self.host_timed_seconds then
+        # excludes the wait for that fill (see include/multigrad_b200.h)
+        timed = C.c_double(0.0)
+        fl_ptr = C.c_void_p(_flush_l2.data_ptr()) if _flush_l2 is not None \
+            else None
+        fl_len = int(_flush_l2.numel()) if _flush_l2 is not None else 0
         rc = plan.lib.mgb_erfbin_adam_host(
             C.byref(plan.model), plan._pt_ref, C.c_void_p(h[0].data_ptr()),
             C.c_void_p(h[1].data_ptr()), m.ctypes.data_as(C.c_void_p),
@@ -347,7 +354,9 @@ class ErfBinnedModel(OnePointModel):
             _adam.ADAM_EPS, traj.ctypes.data_as(C.c_void_p),
             losses.ctypes.data_as(C.c_void_p),
             C.c_void_p(scratch.data_ptr()), scratch.numel(),
-            C.c_void_p(torch.cuda.current_stream().cuda_stream), timeout)
+            C.c_void_p(torch.cuda.current_stream().cuda_stream), timeout,
+            fl_ptr, fl_len, C.byref(timed))
+        self.host_timed_seconds = float(timed.value)
         if rc:
             from ..ops import _lib
             _lib.check(rc, "mgb_erfbin_adam_host")
