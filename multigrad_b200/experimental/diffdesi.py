@@ -26,7 +26,7 @@ def find_ultimate_top_indices(indices):
     if isinstance(indices, torch.Tensor) and indices.is_cuda:
         return _find_top_cuda(indices)
     was_tensor = isinstance(indices, torch.Tensor)
-    idx = np.array(indices.cpu() if was_tensor else indices)
+    idx = indices.cpu().numpy().copy() if was_tensor else np.array(indices)
     count = 0
     while np.any(idx != idx[idx]):
         count += 1
