@@ -261,3 +261,14 @@ def test_checkpoint_resume_roundtrip(tmp_path):
             _quadratic(tgt)(torch.zeros(2), None)
     assert len(timer.times_ms()) == 3
     assert timing.device_time_ms(lambda: None, iters=2, warmup=1) >= 0.0
+
+
+def test_run_adam_host_falls_back_to_generic_on_cpu():
+    """``run_adam_host`` (host-state Adam of the native family) is the plain
+    generic Adam when there is no GPU: same trajectory as ``run_adam``."""
+    from multigrad_b200.models import smf, SMFModel
+    data = smf.make_smf_data(2_000, comm=mg.Comm(None), device="cpu")
+    m = SMFModel(aux_data=data, comm=mg.Comm(None), device="cpu")
+    a = m.run_adam_host([-1.8, 0.3], nsteps=4, learning_rate=0.01)
+    b = m.run_adam([-1.8, 0.3], nsteps=4, learning_rate=0.01)
+    assert a.shape == (5, 2) and torch.allclose(a, b)
