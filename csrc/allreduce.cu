@@ -271,19 +271,23 @@ oneshot_allreduce_f32_kernel(const MgbPeerTable pt, float* __restrict__ data,
       st_peer_f4(slot, v);
     }
   }
-  __threadfence_system();
+  // Release/acquire by the signalling threads only: the CTA barrier makes
+  // every thread's pushes visible to them, their system-scope fence is
+  // cumulative.  (A system fence from all 512 threads costs microseconds.)
   __syncthreads();
   if (tid < W - 1) {
     int dst = me + 1 + tid;
     if (dst >= W) dst -= W;
+    __threadfence_system();
     mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, me, blockIdx.x),
                    (unsigned long long)epoch << 32);
   }
   // ---- wait for the same range of every peer -------------------------------
-  if (tid < W && tid != me)
+  if (tid < W && tid != me) {
     (void)mgb_ll_wait(pt, mgb_ll_slot(pt, me, parity, tid, blockIdx.x), epoch);
+    __threadfence_system();
+  }
   __syncthreads();
-  __threadfence_system();
   // ---- ordered sum ----------------------------------------------------------
   const float4* stage =
       reinterpret_cast<const float4*>((const char*)pt.base[me] + off);

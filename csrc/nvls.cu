@@ -220,18 +220,22 @@ __device__ __forceinline__ void cta_rank_barrier(const MgbPeerTable& pt,
                                                  unsigned unit) {
   const int tid = threadIdx.x, W = pt.world, me = pt.rank;
   const unsigned parity = epoch & 1u;
-  __threadfence_system();
+  // release/acquire by the signalling threads only (cumulative system
+  // fences after / before the CTA barrier): a system fence from all 512
+  // threads costs microseconds per barrier
   __syncthreads();
   if (tid < W - 1) {
     int dst = me + 1 + tid;
     if (dst >= W) dst -= W;
+    __threadfence_system();
     mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, me, unit),
                    (unsigned long long)epoch << 32);
   }
-  if (tid < W && tid != me)
+  if (tid < W && tid != me) {
     (void)mgb_ll_wait(pt, mgb_ll_slot(pt, me, parity, tid, unit), epoch);
+    __threadfence_system();
+  }
   __syncthreads();
-  __threadfence_system();
 }
 
 __device__ __forceinline__ float mc_ld_reduce_f1(const float* p) {
