@@ -1082,6 +1082,89 @@ extern "C" int mgb_erfbin_adam_host(
   return rc;
 }
 
+// Host-driven evaluations with the launch latency hidden, for drivers that
+// call back into Python between evaluations (scipy's L-BFGS-B): a *session*
+// keeps exactly one grid pre-launched and waiting on the GPU for the next
+// parameters (same hand-shake as mgb_erfbin_adam_host).
+//   op 0  begin: reset the hand-shake, queue the first waiting grid
+//   op 1  eval : publish params_host, queue the next waiting grid, poll the
+//                result of this one into out_host[0..P]
+//   op 2  end  : cancel the waiting grid and drain the stream
+// *seq is the session's evaluation counter (owned by the caller, 0 at begin).
+extern "C" int mgb_erfbin_host_session(
+    const MgbErfBinModel* model, const MgbPeerTable* pt, float* params_host,
+    float* out_host, void* scratch, uint64_t scratch_bytes, void* stream,
+    uint32_t timeout_ms, int32_t op, uint32_t* seq) {
+  MGB_REQUIRE(model && params_host && out_host && seq && scratch &&
+                  scratch_bytes >= 256,
+              MGB_EINVAL, "mgb_erfbin_host_session: bad arguments");
+  const int P = model->nparams;
+  MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
+              "mgb_erfbin_host_session: nparams=%d outside [1,%d]", P,
+              MGB_MAX_PARAMS);
+  const uint32_t kSentinel = 0x7fc0deadu;
+  volatile uint32_t* o = reinterpret_cast<volatile uint32_t*>(out_host);
+  volatile uint32_t* flag = o + MGB_HOST_FLAG_WORD;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (op == 2) {
+    __sync_synchronize();
+    *flag = 0x80000000u;
+    MGB_CUDA_CHECK(cudaStreamSynchronize(st));
+    return MGB_OK;
+  }
+  MgbStepArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mode = MGB_MODE_LOSS_GRAD;
+  a.batch = 1;
+  a.reduce = (pt && pt->world > 1) ? 1 : 0;
+  a.params = params_host;
+  a.out_loss = out_host;
+  a.out_grad = out_host + 1;
+  a.wait_flag = const_cast<const uint32_t*>(
+      reinterpret_cast<uint32_t*>(out_host) + MGB_HOST_FLAG_WORD);
+  a.wait_timeout_ms = timeout_ms;
+  if (op == 0) {
+    *flag = 0u;
+    *seq = 0u;
+    MGB_CUDA_CHECK(cudaMemsetAsync(
+        reinterpret_cast<char*>(scratch) + 4 * EB_RELAY_WORD, 0,
+        256 - 4 * EB_RELAY_WORD, st));
+    a.wait_value = 1u;
+    return mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
+  }
+  MGB_REQUIRE(op == 1, MGB_EINVAL, "mgb_erfbin_host_session: bad op %d", op);
+  for (int i = 0; i <= P; ++i) o[i] = kSentinel;
+  __sync_synchronize();
+  *seq += 1u;
+  *flag = *seq;
+  a.wait_value = *seq + 1u;
+  int rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
+  if (rc != MGB_OK) return rc;
+  struct timespec t0;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (unsigned spin = 0;; ++spin) {
+    bool done = true;
+    for (int i = 0; i <= P; ++i) done = done && (o[i] != kSentinel);
+    if (done) break;
+    if ((spin & 0x3ffu) == 0x3ffu) {
+      struct timespec t1;
+      clock_gettime(CLOCK_MONOTONIC, &t1);
+      const double ms = (t1.tv_sec - t0.tv_sec) * 1e3 +
+                        (t1.tv_nsec - t0.tv_nsec) * 1e-6;
+      if (ms > (double)timeout_ms) {
+        mgb_set_error("mgb_erfbin_host_session: no result after %u ms",
+                      timeout_ms);
+        return MGB_ESTATE;
+      }
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+  __sync_synchronize();
+  return MGB_OK;
+}
+
 // Root side of one multi-GPU L-BFGS-B evaluation in ONE native call (K6):
 // gate + parameters (pinned host) -> device control block, LL broadcast of the
 // block to the workers' GPUs over NVLink, gated fused loss+gradient launch

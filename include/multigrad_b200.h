@@ -210,6 +210,16 @@ int mgb_erfbin_eval_host_zc(const MgbErfBinModel* model,
  * multigrad/adam.py:52-68) without a Python round trip per step: nsteps x
  * [zero-copy evaluation, Adam update in host memory].  params_host/out_host
  * pinned; traj ((nsteps+1) x P, row 0 = start) and loss_hist may be NULL. */
+/* Session of host-driven evaluations with one grid always pre-launched and
+ * waiting on the GPU (hides the launch latency for drivers that return to
+ * Python between evaluations, e.g. scipy's L-BFGS-B).  op: 0 begin, 1 eval
+ * (params_host -> out_host[0..P]), 2 end.  out_host as for
+ * mgb_erfbin_adam_host; *seq is the caller-owned evaluation counter. */
+int mgb_erfbin_host_session(const MgbErfBinModel* model,
+                            const MgbPeerTable* pt, float* params_host,
+                            float* out_host, void* scratch,
+                            uint64_t scratch_bytes, void* stream,
+                            uint32_t timeout_ms, int32_t op, uint32_t* seq);
 /* Root side of one multi-GPU L-BFGS-B evaluation (K6) in one call: control
  * block (gate, params; pinned host) -> device, LL broadcast to the workers,
  * gated fused launch writing (loss, grad) into pinned out_host, poll.  With

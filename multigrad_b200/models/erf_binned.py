@@ -502,14 +502,64 @@ class ErfBinnedModel(OnePointModel):
         def callback(*_a, **_k):
             if hasattr(pbar, "update"):
                 pbar.update()
+        fn, end_session = self._host_session(x0)
         try:
             return scipy.optimize.minimize(
-                self.loss_and_grad_host, x0=x0, method="L-BFGS-B", jac=True,
+                fn, x0=x0, method="L-BFGS-B", jac=True,
                 options=dict(maxiter=maxsteps), callback=callback,
                 bounds=param_bounds)
         finally:
+            end_session()
             if hasattr(pbar, "close"):
                 pbar.close()
+
+    def _host_session(self, warm_params):
+        """``(evaluate, end)``: host-driven loss+gradient evaluations with
+        one grid always pre-launched and waiting on the GPU for the next
+        parameters (``mgb_erfbin_host_session``), so that a driver which
+        returns to Python between evaluations -- scipy's L-BFGS-B -- does not
+        pay the launch latency each time.  ``end()`` must be called (it
+        cancels the waiting grid).  With ``MULTIGRAD_B200_HOST_PIPELINE=0``
+        this is plain ``loss_and_grad_host``."""
+        if os.environ.get("MULTIGRAD_B200_HOST_PIPELINE", "1") == "0":
+            return self.loss_and_grad_host, (lambda: None)
+        import ctypes as C
+        plan = self.plan()
+        P = self.nparams
+        if self._host is None:
+            self.loss_and_grad_host(warm_params)        # creates the buffers
+        h = self._host
+        seq = C.c_uint32(0)
+        timeout = 60000
+        if plan.pt is not None:
+            timeout = max(timeout, 2 * int(plan.pt.spin_timeout_ms))
+        if torch.cuda.current_device() != self.device.index:
+            torch.cuda.set_device(self.device)
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        base = (C.byref(plan.model), plan._pt_ref,
+                C.c_void_p(h[0].data_ptr()), C.c_void_p(h[1].data_ptr()),
+                C.c_void_p(h[4].data_ptr()), h[4].numel(), stream, timeout)
+        session = plan.lib.mgb_erfbin_host_session
+        from ..ops import _lib, erfbin as _eb
+
+        def call(op):
+            rc = session(*base, op, C.byref(seq))
+            if rc:
+                _lib.check(rc, "mgb_erfbin_host_session")
+
+        call(0)
+        n_in, n_out = h[5], h[6]
+
+        def evaluate(p):
+            n_in[:] = p
+            call(1)
+            _eb._LAUNCHES += 1
+            return float(n_out[0]), n_out[1:1 + P].astype(np.float64)
+
+        def end():
+            call(2)
+
+        return evaluate, end
 
     def run_lhs_param_scan(self, xmins, xmaxs, n_dim, num_evaluations,
                            seed=None, randkey=None):

@@ -222,6 +222,10 @@ def _declare(lib: C.CDLL) -> None:
         i32, i32, f32, f32, f32, f32, vp, vp, vp, u64, vp, u32, vp, u64,
         C.POINTER(C.c_double)]
     lib.mgb_erfbin_adam_host.restype = C.c_int
+    lib.mgb_erfbin_host_session.argtypes = [
+        C.POINTER(MgbErfBinModel), C.POINTER(MgbPeerTable), vp, vp, vp, u64,
+        vp, u32, i32, C.POINTER(u32)]
+    lib.mgb_erfbin_host_session.restype = C.c_int
     lib.mgb_erfbin_bfgs_root_eval.argtypes = [
         C.POINTER(MgbErfBinModel), C.POINTER(MgbPeerTable), vp, vp, vp, vp,
         u64, vp, u32]
