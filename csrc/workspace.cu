@@ -16,6 +16,19 @@ void mgb_set_error(const char* fmt, ...) {
 extern "C" const char* mgb_last_error(void) { return g_err; }
 extern "C" int mgb_version(void) { return 100; }
 
+// sizeof of every by-value struct of the C ABI, in declaration order, so that
+// a binding can detect a stale mirror at load time instead of corrupting
+// kernel arguments.
+extern "C" int mgb_abi_sizes(uint32_t* out, int n) {
+  const uint32_t sizes[] = {
+      (uint32_t)sizeof(MgbPeerTable), (uint32_t)sizeof(MgbErfBinModel),
+      (uint32_t)sizeof(MgbStepArgs),  (uint32_t)sizeof(MgbGroupArgs),
+      (uint32_t)sizeof(MgbLinModel),  (uint32_t)sizeof(MgbLinArgs)};
+  const int have = (int)(sizeof(sizes) / sizeof(sizes[0]));
+  for (int i = 0; i < n && i < have; ++i) out[i] = sizes[i];
+  return have;
+}
+
 extern "C" uint64_t mgb_ws_bytes(int world, uint32_t ll_units,
                                  uint64_t bulk_bytes) {
   // two bulk regions + a flag page per region

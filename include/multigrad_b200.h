@@ -51,6 +51,11 @@ typedef struct MgbPeerTable {
   void* base[MGB_MAX_WORLD];/* workspace base of every rank (peer-mapped)    */
 } MgbPeerTable;
 
+/* sizeof(MgbPeerTable, MgbErfBinModel, MgbStepArgs, MgbGroupArgs, MgbLinModel,
+ * MgbLinArgs) -> out[0..n); returns how many there are.  Bindings compare
+ * these with their own mirrors when they load the library. */
+int mgb_abi_sizes(uint32_t* out, int n);
+
 uint64_t mgb_ws_bytes(int world, uint32_t ll_units, uint64_t bulk_bytes);
 int mgb_ws_alloc(uint64_t bytes, void** out_ptr);
 int mgb_ws_free(void* ptr);

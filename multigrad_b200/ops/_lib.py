@@ -281,8 +281,32 @@ def load(build_if_missing: bool = True) -> C.CDLL:
     override = os.environ.get("MULTIGRAD_B200_LIB")   # tuning experiments
     lib = C.CDLL(override if override else str(LIB_PATH))
     _declare(lib)
+    _check_abi(lib)
     _LIB = lib
     return lib
+
+
+def _check_abi(lib: C.CDLL) -> None:
+    """The ctypes mirrors must have the size the library was compiled with:
+    a stale mirror would silently corrupt kernel arguments."""
+    if not hasattr(lib, "mgb_abi_sizes"):
+        return                      # experimental build without the query
+    from . import linlink as _ll    # mirrors of the linear-link structs
+    mirrors = [("MgbPeerTable", MgbPeerTable),
+               ("MgbErfBinModel", MgbErfBinModel),
+               ("MgbStepArgs", MgbStepArgs), ("MgbGroupArgs", MgbGroupArgs),
+               ("MgbLinModel", _ll.MgbLinModel),
+               ("MgbLinArgs", _ll.MgbLinArgs)]
+    out = (C.c_uint32 * len(mirrors))()
+    lib.mgb_abi_sizes.argtypes = [C.POINTER(C.c_uint32), C.c_int]
+    lib.mgb_abi_sizes.restype = C.c_int
+    n = lib.mgb_abi_sizes(out, len(mirrors))
+    for i, (name, cls) in enumerate(mirrors[:n]):
+        if int(out[i]) != C.sizeof(cls):
+            raise MgbError(
+                f"ABI mismatch: sizeof({name}) is {int(out[i])} in "
+                f"libmgb200.so but {C.sizeof(cls)} in the Python mirror "
+                "(rebuild the library or update the mirror)")
 
 
 def available() -> bool:
