@@ -24,7 +24,7 @@ Design differences (SURVEY.md sections 2.3, 9):
 from __future__ import annotations
 
 import math
-from typing import Any, NamedTuple, Optional, Sequence
+from typing import Any, NamedTuple, Optional
 
 import numpy as np
 import torch

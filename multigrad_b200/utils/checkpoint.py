@@ -9,7 +9,7 @@ identical values, so only rank 0 needs to write.
 from __future__ import annotations
 
 import os
-from typing import Optional, Tuple
+from typing import Optional
 
 import numpy as np
 import torch

@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import contextlib
 import time
-from typing import Callable, List, Optional
+from typing import Callable, List
 
 import torch
 
