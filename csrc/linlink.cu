@@ -556,7 +556,12 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
                                    (~__float_as_uint(zs[e]) & 0x80000000u));
         accO[e] += (int)(__float_as_uint(zs[e]) >> 31);
         accZ[e] = fmaf(zs[e], g[e], accZ[e]);
-        // g -> two bf16 planes, rows (edge) and (16 + edge), column = object.
+        // g -> two bf16 planes, column = object: the hi plane in row `edge`,
+        // the lo plane in row 16 + (edge ^ 4).  The ^4 moves the lo word of a
+        // lane pair four 16-byte chunks away from the hi word inside the
+        // SW128 pattern; with 16 + edge both land in the same bank (rows 16
+        // apart share r % 8) and every store is a 2-way conflict (ncu: 52% of
+        // the shared-store wavefronts were conflicts).
         // Lanes pair up so that every lane issues one full-word store: the
         // even lane writes the g_hi pair, the odd lane the g_lo pair
         // (2-byte stores from all 32 lanes cost 3x the wavefronts; ncu).
@@ -571,7 +576,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
                                   : ((mine >> 16) | (other & 0xffff0000u));
         if (!(LL_ABL & 2))
           *reinterpret_cast<uint32_t*>(
-              gs + sw128_offset_16b(odd ? 16u + r : r, ko & ~1u)) = word;
+              gs + sw128_offset_16b(odd ? 16u + (r ^ 4u) : r, ko & ~1u)) = word;
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -650,8 +655,9 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       val = s_edge[k + 1][2] - s_edge[k][2];
     } else {
       const int k = (j - 2 * K) / P, f = (j - 2 * K) - k * P;
-      const double hi1 = s_gw[(k + 1) * P + f], lo1 = s_gw[(17 + k) * P + f];
-      const double hi0 = s_gw[k * P + f], lo0 = s_gw[(16 + k) * P + f];
+      const double hi1 = s_gw[(k + 1) * P + f];
+      const double lo1 = s_gw[(16 + ((k + 1) ^ 4)) * P + f];
+      const double hi0 = s_gw[k * P + f], lo0 = s_gw[(16 + (k ^ 4)) * P + f];
       val = (hi1 - hi0) + (lo1 - lo0);
     }
     partials[(size_t)blockIdx.x * M + j] = val;
