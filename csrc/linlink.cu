@@ -63,6 +63,9 @@ constexpr int LL_TILE = 128;     // objects per tile (UMMA M of #1, K of #2)
 constexpr int LL_FB = 64;        // features per 128-byte swizzle block
 constexpr int LL_GROWS = 32;     // rows of G: 16 x g_hi, 16 x g_lo
 
+#ifndef LL_SWAP
+#define LL_SWAP 1
+#endif
 #ifndef LL_IDLE_SLEEP_NS
 #define LL_IDLE_SLEEP_NS 0
 #endif
@@ -397,7 +400,15 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       // M = 64: only 32 rows of G are meaningful; the 64-row form halves the
       // operand fetch.  Its accumulator rows r land in TMEM lane
       // 32*(r/16) + r%16 (probed with tools/probe_m64.py).
+#if LL_SWAP
+      // Jacobian product with the operands swapped: D2[P x 32] += Wt . Gt,
+      // A = W tile read MN-major (M = features), B = G read K-major
+      // (N = 32 rows): 3 KiB (P = 64) / 5 KiB (P = 128) of operand fetch per
+      // instruction instead of 4 / 6 KiB, and no zero-padded half of G.
+      const uint32_t id2 = idesc_bf16_f32(P, LL_GROWS, true, false);
+#else
       const uint32_t id2 = idesc_bf16_f32(64, P, false, true);
+#endif
       const uint64_t dk = smem_desc_sw128(0, 16, 1024);                // K-major
       const uint64_t dmn = smem_desc_sw128(0, LL_TILE * 128, 1024);    // MN-major
       const uint64_t th0 = dk + (smem_u32(s_th) >> 4);
@@ -444,10 +455,17 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
 #pragma unroll
               for (int kstep = 0; kstep < ((LL_ABL & 1) ? 0 : LL_TILE / 16);
                    ++kstep) {
+#if LL_SWAP
+                umma_bf16(tm_d2 + (kstep % NACC) * LL_GROWS,
+                          b0 + kstep * (2048 / 16),
+                          a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
+                          id2, !first || kstep >= NACC);
+#else
                 umma_bf16(tm_d2 + (kstep % NACC) * P,
                           a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
                           b0 + kstep * (2048 / 16), id2,
                           !first || kstep >= NACC);
+#endif
               }
               umma_commit(&empty[s]);
               LL_TR(7, n2);
@@ -612,6 +630,40 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   }
   // ---- D2 (TMEM) -> shared: rows 0..15 g_hi, 16..31 g_lo, P columns -------
   float* s_gw = reinterpret_cast<float*>(smem);   // pipeline buffers are dead
+#if LL_SWAP
+  if (warp >= 4 && warp < 8) {
+    // D2 is [feature -> TMEM lane][G row -> column].  Warp 4+q owns lanes
+    // 32q..32q+31.  M = 128 (P = 128): lane = feature.  M = 64 (P = 64):
+    // feature f sits in lane 32*(f/16) + f%16, lanes 16..31 of a quadrant
+    // are unused.
+    const int q = warp - 4;
+    int okw = 1;
+    if (my_tiles > 0) okw = mbar_wait(&d2_done, 0);
+    tc_fence_after();
+    const int f = (P == 64) ? 16 * q + lane : 32 * q + lane;
+    const bool has_f = (P == 64) ? lane < 16 : true;
+    for (int c = 0; c < LL_GROWS; c += 16) {
+      float accv[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) accv[i] = 0.f;
+      if (my_tiles > 0) {
+        for (int ac = 0; ac < NACC; ++ac) {
+          uint32_t v[16];
+          tmem_ld_x16(tm_d2 + ac * LL_GROWS + c + ((uint32_t)(q * 32) << 16),
+                      v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) accv[i] += __uint_as_float(v[i]);
+        }
+      }
+      if (has_f) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s_gw[(c + i) * P + f] = accv[i];
+      }
+    }
+    if (!okw) atomicExch(&s_fail, 1);
+  }
+#else
   if (warp == 4 || warp == 5) {
     // warp 4 owns TMEM lanes 0..31 (rows 0..15 = g_hi in lanes 0..15),
     // warp 5 lanes 32..63 (rows 16..31 = g_lo in lanes 32..47)
@@ -640,6 +692,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
     }
     if (!okw) atomicExch(&s_fail, 1);
   }
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
