@@ -277,7 +277,16 @@ constexpr int LL_MAX_STAGES = 8;
 // (64 x P x 16), so a single accumulator chain is bound by the ~95-cycle
 // accumulate latency; K steps are dealt round-robin to LL_NACC chains that
 // are summed at read-out
+#if LL_SWAP
+// (swapped form: an accumulator is only 32 columns wide, so every K step of a
+// tile gets its own one: 8 x 32 columns from column 128)
+#ifndef LL_NACC_SWAP
+#define LL_NACC_SWAP 8
+#endif
+__host__ __device__ constexpr int ll_nacc(int) { return LL_NACC_SWAP; }
+#else
 __host__ __device__ constexpr int ll_nacc(int P) { return P <= 64 ? 4 : 2; }
+#endif
 constexpr int LL_SETS = 2;          // compute-warp sets; set k owns tiles it%2==k
 constexpr int LL_CWARPS = 12;       // compute warps per set
 constexpr int LL_THREADS = 32 * (2 + LL_SETS * LL_CWARPS);   // 832
