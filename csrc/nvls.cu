@@ -23,25 +23,83 @@
 #include <string.h>
 #include "mgb_common.cuh"
 
+
+namespace {
+
+// The driver API is reached through cudaGetDriverEntryPoint, never through a
+// link-time symbol: libmgb200.so must stay loadable on a machine without
+// libcuda.so.1 (the CPU-only build check imports the library).
+#define MGB_DRV_LIST(X)                                                       \
+  X(cuDeviceGet)                                                 \
+  X(cuDeviceGetAttribute)                                        \
+  X(cuGetErrorString)                                            \
+  X(cuMulticastGetGranularity)                                   \
+  X(cuMemGetAllocationGranularity)                               \
+  X(cuMulticastCreate)                                           \
+  X(cuMemExportToShareableHandle)                                \
+  X(cuMemImportFromShareableHandle)                              \
+  X(cuMulticastAddDevice)                                        \
+  X(cuMemCreate)                                                 \
+  X(cuMulticastBindMem)                                          \
+  X(cuMemAddressReserve)                                         \
+  X(cuMemMap)                                                    \
+  X(cuMemSetAccess)                                              \
+  X(cuMemUnmap)                                                  \
+  X(cuMemAddressFree)                                            \
+  X(cuMulticastUnbind)                                           \
+  X(cuMemRelease)
+
+struct Drv {
+#define MGB_DRV_MEMBER(name) decltype(&name) p_##name = nullptr;
+  MGB_DRV_LIST(MGB_DRV_MEMBER)
+#undef MGB_DRV_MEMBER
+  bool ok = false;
+};
+
+Drv& drv() {
+  static Drv d;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    bool all = true;
+#define MGB_DRV_LOAD(name)                                                    \
+    {                                                                         \
+      void* fn = nullptr;                                                     \
+      cudaDriverEntryPointQueryResult q;                                      \
+      if (cudaGetDriverEntryPoint(#name, &fn, cudaEnableDefault, &q) !=       \
+              cudaSuccess ||                                                  \
+          fn == nullptr || q != cudaDriverEntryPointSuccess)                  \
+        all = false;                                                          \
+      d.p_##name = reinterpret_cast<decltype(d.p_##name)>(fn);                \
+    }
+    MGB_DRV_LIST(MGB_DRV_LOAD)
+#undef MGB_DRV_LOAD
+    d.ok = all;
+  }
+  return d;
+}
+
+
 #define MGB_CU_CHECK(expr)                                                    \
   do {                                                                        \
     CUresult _r = (expr);                                                     \
     if (_r != CUDA_SUCCESS) {                                                 \
       const char* _s = nullptr;                                               \
-      cuGetErrorString(_r, &_s);                                              \
+      drv().p_cuGetErrorString(_r, &_s);                                              \
       mgb_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,             \
                     _s ? _s : "unknown CUresult");                            \
       return MGB_ESTATE;                                                      \
     }                                                                         \
   } while (0)
 
-namespace {
-
 int current_device(CUdevice* dev, int* ordinal) {
   int d = 0;
   MGB_CUDA_CHECK(cudaGetDevice(&d));
   MGB_CUDA_CHECK(cudaFree(0));          // make sure the primary context exists
-  MGB_CU_CHECK(cuDeviceGet(dev, d));
+  MGB_REQUIRE(drv().ok, MGB_ESTATE,
+              "the CUDA driver does not export the virtual-memory / multicast "
+              "entry points (cudaGetDriverEntryPoint failed)");
+  MGB_CU_CHECK(drv().p_cuDeviceGet(dev, d));
   if (ordinal) *ordinal = d;
   return MGB_OK;
 }
@@ -63,7 +121,7 @@ extern "C" int mgb_mc_supported(int* out) {
   int rc = current_device(&dev, nullptr);
   if (rc != MGB_OK) return rc;
   int v = 0;
-  MGB_CU_CHECK(cuDeviceGetAttribute(
+  MGB_CU_CHECK(drv().p_cuDeviceGetAttribute(
       &v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev));
   *out = v;
   return MGB_OK;
@@ -74,7 +132,7 @@ extern "C" int mgb_mc_round_size(int world, uint64_t bytes, uint64_t* out) {
   MGB_REQUIRE(out && world >= 2, MGB_EINVAL, "mgb_mc_round_size: bad args");
   CUmulticastObjectProp p = mc_prop(world, bytes);
   size_t gran = 0;
-  MGB_CU_CHECK(cuMulticastGetGranularity(&gran, &p,
+  MGB_CU_CHECK(drv().p_cuMulticastGetGranularity(&gran, &p,
                                          CU_MULTICAST_GRANULARITY_MINIMUM));
   // the physical allocation must satisfy its own granularity too
   CUdevice dev;
@@ -88,7 +146,7 @@ extern "C" int mgb_mc_round_size(int world, uint64_t bytes, uint64_t* out) {
   ap.location.id = ord;
   ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
   size_t g2 = 0;
-  MGB_CU_CHECK(cuMemGetAllocationGranularity(
+  MGB_CU_CHECK(drv().p_cuMemGetAllocationGranularity(
       &g2, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
   if (g2 > gran) gran = g2;
   *out = (bytes + gran - 1) / gran * gran;
@@ -104,9 +162,9 @@ extern "C" int mgb_mc_create(int world, uint64_t bytes, uint64_t* handle_out,
   if (rc != MGB_OK) return rc;
   CUmulticastObjectProp p = mc_prop(world, bytes);
   CUmemGenericAllocationHandle h;
-  MGB_CU_CHECK(cuMulticastCreate(&h, &p));
+  MGB_CU_CHECK(drv().p_cuMulticastCreate(&h, &p));
   int fd = -1;
-  MGB_CU_CHECK(cuMemExportToShareableHandle(
+  MGB_CU_CHECK(drv().p_cuMemExportToShareableHandle(
       &fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
   *handle_out = (uint64_t)h;
   *fd_out = fd;
@@ -119,7 +177,7 @@ extern "C" int mgb_mc_import(int fd, uint64_t* handle_out) {
   int rc = current_device(&dev, nullptr);
   if (rc != MGB_OK) return rc;
   CUmemGenericAllocationHandle h;
-  MGB_CU_CHECK(cuMemImportFromShareableHandle(
+  MGB_CU_CHECK(drv().p_cuMemImportFromShareableHandle(
       &h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
   *handle_out = (uint64_t)h;
   return MGB_OK;
@@ -129,7 +187,7 @@ extern "C" int mgb_mc_add_device(uint64_t handle) {
   CUdevice dev;
   int rc = current_device(&dev, nullptr);
   if (rc != MGB_OK) return rc;
-  MGB_CU_CHECK(cuMulticastAddDevice((CUmemGenericAllocationHandle)handle, dev));
+  MGB_CU_CHECK(drv().p_cuMulticastAddDevice((CUmemGenericAllocationHandle)handle, dev));
   return MGB_OK;
 }
 
@@ -150,20 +208,20 @@ extern "C" int mgb_mc_bind(uint64_t handle, uint64_t bytes, void** uc_out,
   ap.location.id = ord;
   ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
   CUmemGenericAllocationHandle mem;
-  MGB_CU_CHECK(cuMemCreate(&mem, bytes, &ap, 0));
-  MGB_CU_CHECK(cuMulticastBindMem(mc, 0, mem, 0, bytes, 0));
+  MGB_CU_CHECK(drv().p_cuMemCreate(&mem, bytes, &ap, 0));
+  MGB_CU_CHECK(drv().p_cuMulticastBindMem(mc, 0, mem, 0, bytes, 0));
   CUmemAccessDesc acc;
   memset(&acc, 0, sizeof(acc));
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = ord;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
   CUdeviceptr uc = 0, mcva = 0;
-  MGB_CU_CHECK(cuMemAddressReserve(&uc, bytes, 0, 0, 0));
-  MGB_CU_CHECK(cuMemMap(uc, bytes, 0, mem, 0));
-  MGB_CU_CHECK(cuMemSetAccess(uc, bytes, &acc, 1));
-  MGB_CU_CHECK(cuMemAddressReserve(&mcva, bytes, 0, 0, 0));
-  MGB_CU_CHECK(cuMemMap(mcva, bytes, 0, mc, 0));
-  MGB_CU_CHECK(cuMemSetAccess(mcva, bytes, &acc, 1));
+  MGB_CU_CHECK(drv().p_cuMemAddressReserve(&uc, bytes, 0, 0, 0));
+  MGB_CU_CHECK(drv().p_cuMemMap(uc, bytes, 0, mem, 0));
+  MGB_CU_CHECK(drv().p_cuMemSetAccess(uc, bytes, &acc, 1));
+  MGB_CU_CHECK(drv().p_cuMemAddressReserve(&mcva, bytes, 0, 0, 0));
+  MGB_CU_CHECK(drv().p_cuMemMap(mcva, bytes, 0, mc, 0));
+  MGB_CU_CHECK(drv().p_cuMemSetAccess(mcva, bytes, &acc, 1));
   MGB_CUDA_CHECK(cudaMemset((void*)uc, 0, bytes));
   MGB_CUDA_CHECK(cudaDeviceSynchronize());
   *uc_out = (void*)uc;
@@ -178,17 +236,17 @@ extern "C" int mgb_mc_release(uint64_t handle, uint64_t mem, void* uc,
   int rc = current_device(&dev, nullptr);
   if (rc != MGB_OK) return rc;
   if (mc) {
-    cuMemUnmap((CUdeviceptr)mc, bytes);
-    cuMemAddressFree((CUdeviceptr)mc, bytes);
+    drv().p_cuMemUnmap((CUdeviceptr)mc, bytes);
+    drv().p_cuMemAddressFree((CUdeviceptr)mc, bytes);
   }
   if (uc) {
-    cuMemUnmap((CUdeviceptr)uc, bytes);
-    cuMemAddressFree((CUdeviceptr)uc, bytes);
+    drv().p_cuMemUnmap((CUdeviceptr)uc, bytes);
+    drv().p_cuMemAddressFree((CUdeviceptr)uc, bytes);
   }
   if (handle && mem)
-    cuMulticastUnbind((CUmemGenericAllocationHandle)handle, dev, 0, bytes);
-  if (mem) cuMemRelease((CUmemGenericAllocationHandle)mem);
-  if (handle) cuMemRelease((CUmemGenericAllocationHandle)handle);
+    drv().p_cuMulticastUnbind((CUmemGenericAllocationHandle)handle, dev, 0, bytes);
+  if (mem) drv().p_cuMemRelease((CUmemGenericAllocationHandle)mem);
+  if (handle) drv().p_cuMemRelease((CUmemGenericAllocationHandle)handle);
   return MGB_OK;
 }
 

@@ -169,7 +169,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         objs = list(ex.map(compile_one, srcs))
     tmp = LIB_PATH.with_suffix(".so.tmp%d" % os.getpid())
     cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a",
-           "-o", str(tmp), *map(str, objs), "-lcuda"]
+           "-o", str(tmp), *map(str, objs)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}{r.stderr}")

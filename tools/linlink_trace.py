@@ -31,7 +31,7 @@ def build():
     subprocess.run(
         ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "-O3", "-std=c++17", "-Xcompiler", "-fPIC", "-DLL_TRACE", "-I",
-         str(ROOT / "include"), "-shared", "-o", str(LIB), *srcs, "-lcuda"],
+         str(ROOT / "include"), "-shared", "-o", str(LIB), *srcs],
         check=True)
 
 
