@@ -44,3 +44,22 @@ def test_struct_sizes_and_offsets_match_the_header(tmp_path):
         for field, _ in cls._fields_:
             assert int(got[f"{name}.{field}"]) == getattr(cls, field).offset, \
                 f"{name}.{field}"
+
+
+@pytest.mark.skipif(_lib.nvcc_path() is None, reason="needs nvcc to build")
+def test_library_loads_without_a_gpu_driver():
+    """``__graft_entry__.build()`` imports the library on a machine without
+    ``libcuda.so.1``: the driver API must only be reached through
+    ``cudaGetDriverEntryPoint`` (csrc/nvls.cu, csrc/linlink.cu), never through
+    a link-time symbol."""
+    path = _lib.build()
+    if shutil.which("readelf"):
+        dyn = subprocess.run(["readelf", "-d", str(path)], check=True,
+                             capture_output=True, text=True).stdout
+        assert "libcuda" not in dyn, dyn
+    lib = _lib.load()                  # also runs the ABI size check
+    assert lib.mgb_version() >= 100
+    out = (C.c_uint32 * 8)()
+    assert lib.mgb_abi_sizes(out, 8) == len(MIRRORS)
+    assert [int(v) for v in out[:len(MIRRORS)]] == \
+        [C.sizeof(cls) for _, cls in MIRRORS]
