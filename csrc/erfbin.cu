@@ -2,28 +2,43 @@
 // cross-GPU reduction + loss / chain rule / optimiser epilogue.  sm_100a.
 //
 // What one launch does (see include/multigrad_b200.h for the contract):
-//   main loop   every thread streams objects (float4 loads), and for each of
-//               the E = K+1 bin edges evaluates, on packed fp32x2 lanes
-//               (FFMA2/FADD2/FMUL2, two objects per instruction),
+//   main loop   every thread streams objects (float4 loads) and, for each of
+//               the edges of its warp's edge group, evaluates on packed fp32x2
+//               lanes (FFMA2/FMUL2, two objects per instruction)
 //                   zs  = kappa*(edge - mu)/(sqrt2*sigma)      (kappa^2 = log2 e)
-//                   g   = 2^(-zs^2) = exp(-z^2)               (MUFU.EX2)
+//                   g   = 2^(-zs^2) = exp(-z^2)
 //                   q   = 1/2 erfc(|z|) = g * t*P(t)/2, t = 1/(1+|z|/2) (MUFU.RCP)
 //               and accumulates per edge  T = sum -+q (tail part of the CDF),
-//               O = sum [z>=0] (hard count), G = sum g, Z = sum zs*g.
+//               O = sum [z>=0] (hard count), G = sum g, Z' = sum zs_centre*g.
 //               Phi = O + T exactly, so bin sums never subtract numbers near 1.
-//   CTA reduce  warp shuffles in fp32, cross-warp and everything after in fp64;
-//               per-CTA partial (D_k, dG_k, dZ_k) goes to `scratch`.
-//   grid reduce the last CTA (atomic ticket) sums the partials in a fixed
-//               order -> run-to-run deterministic.
+//               Uniformly spaced edges: only every (2L+1)-th edge (an anchor)
+//               gets its Gaussian from MUFU.EX2; its neighbours follow by a
+//               multiplicative recurrence
+//                   g_{e+1} = g_e * rho_e,   rho_{e+1} = rho_e * 2^(-2 d^2)
+//               Tiles with an object too far from the group's central edge
+//               for that to be accurate, and non-uniform edges, take the
+//               per-edge MUFU.EX2 path.
+//   CTA reduce  warp shuffles in fp32, cross-warp and everything after in fp64.
+//   cluster     the CTAs of a thread-block cluster push their 3K partial sums
+//               into the leader CTA's shared memory (DSMEM, st.shared::cluster)
+//               and the leader adds them in rank order: one global partial
+//               per cluster instead of one per CTA.
+//   grid reduce the last cluster leader (atomic ticket) sums the partials in a
+//               fixed order -> run-to-run deterministic.
 //   GPU reduce  the same CTA pushes the 3K doubles to every peer with the LL
 //               protocol over NVLink and sums in rank order (mgb_common.cuh).
 //   epilogue    sumstats, Jacobian, loss, dL/ds, gradient, bound-transform
 //               chain rule and the Adam / GD update, trajectory + loss rows.
+//   persistent  with args.nsteps > 1 all of the above repeats inside ONE
+//               launch: the other CTAs wait on the device for the step counter
+//               and re-read the parameters (their first tile already in
+//               registers).
 //
 // Reference counterparts: OnePointModel._vjp (multigrad/multigrad.py:508-538),
 // calc_smf_bin (tests/smf_example/smf_grad_descent.py:38-48), _adam_optimizer
 // (multigrad/adam.py:52-68), transforms (adam.py:192-239), simple_grad_descent
-// (multigrad/util.py:100-114).
+// (multigrad/util.py:100-114), and for the persistent form the in-scan
+// collectives of multigrad/mpi4jax/multigrad.py:38-58.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -34,18 +49,16 @@
 
 #define EB_SENTINEL_X 1.0e30f // padding object: contributes exactly zero
 
-// word of the counter block used as host-hand-shake relay (batch == 1 only:
-// the block is 64 words, the ticket counter is word 0)
-#define EB_RELAY_WORD 32
+// words of the counter block (the block is 64 words; tickets are words
+// [0, batch), the others are only used with batch == 1)
+#define EB_RELAY_WORD 32      // host hand-shake relay (token + parameters)
+#define EB_ABORT_WORD 24      // persistent fit: a step failed, everybody leave
 #ifndef EB_HOST_POLL_NS
 #define EB_HOST_POLL_NS 100
 #endif
 
 namespace {
 
-struct F2 {
-  float2 v;
-};
 __device__ __forceinline__ float2 f2(float a, float b) {
   return make_float2(a, b);
 }
@@ -75,108 +88,269 @@ __device__ __forceinline__ float2 vfma(float2 a, float2 b, float2 c) {
 // kappa = sqrt(log2(e)): exp(-z^2) == 2^(-(kappa z)^2)
 #define EB_KAPPA 1.2011224087864498f
 #define EB_INV_KAPPA 0.8325546111576977
-// t = 1/(1 + c |z|) = 1/(1 + (c/kappa) |zs|), c = MGB_ERFCX_CSCALE
+// t = 1/(1 + c |z|) = 1/(1 + |w|), w = (c/kappa) zs, c = MGB_ERFCX_CSCALE
 #define EB_HSCALE (MGB_ERFCX_CSCALE / EB_KAPPA)
-#define EB_ZS_SKIP 12.4f  // |zs| beyond which g and q flush to zero
+#define EB_ZS_SKIP 12.4f   // |zs| beyond which g and q flush to zero
+// Gaussian recurrence: used for a tile while every object is within za_lim of
+// the group's central edge (in zs units), za_lim = min(EB_ZA_MAX,
+// (EB_CHAIN_EXP_MAX - (ET+1) d^2) / (2 d)): the exponent of every ratio then
+// stays below EB_CHAIN_EXP_MAX in magnitude, which bounds the relative error
+// a ratio inherits from the fp32 rounding of its exponent to
+// EB_CHAIN_EXP_MAX * 2^-24 * ln 2 = 6.6e-7 (and keeps everything finite).
+#define EB_ZA_MAX 10.0f
+#define EB_CHAIN_EXP_MAX 16.0
+
+// ------------------------------------------------------------ cluster / DSMEM
+__device__ __forceinline__ unsigned eb_cluster_ctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned eb_cluster_nctarank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void eb_cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void eb_cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `p` (a shared-memory object of this kernel) in
+// the CTA of rank `rank` of this cluster
+__device__ __forceinline__ unsigned eb_mapa(const void* p, unsigned rank) {
+  unsigned a = (unsigned)__cvta_generic_to_shared(p), r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r)
+               : "r"(a), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void eb_st_cluster_f64(unsigned addr, double v) {
+  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v)
+               : "memory");
+}
+__device__ __forceinline__ int eb_ld_acquire_gpu_s32(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void eb_st_release_gpu_s32(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v)
+               : "memory");
+}
 
 // Per-edge accumulators are scalar: a packed FADD2 and two FADDs cost the
-// same FMA-pipe time (the pipe retires 32 fp32 lanes per cycle either way) and
-// the issue slots are not the limiter, while four registers per edge are what
-// lets ptxas keep ET independent Horner chains in flight.
+// same FMA-pipe time and four registers per edge are what lets ptxas keep the
+// edges' Horner chains in flight together.
 struct EdgeAcc {
   float T, O, G, Z;
 };
 
-// Contribution of a pair of objects (centred coordinate xc, weight wt) to the
-// accumulators of the ET edges of a group, zs_e = cs_e - ks*xc.
+#ifndef EB_CHAIN_LEN
+#define EB_CHAIN_LEN 2
+#endif
+// Segments of S = 2*EB_CHAIN_LEN + 1 consecutive edges of a group of ET edges;
+// the middle edge of a segment is its anchor.
+template <int ET>
+struct EbSeg {
+  static constexpr int S = 2 * EB_CHAIN_LEN + 1 < ET ? 2 * EB_CHAIN_LEN + 1
+                                                     : ET;
+  static constexpr int NSEG = (ET + S - 1) / S;
+  static constexpr int A0 = ET / 2;  // central edge: Z' anchor, base ratios
+  __host__ __device__ static constexpr int first(int sg) { return sg * S; }
+  __host__ __device__ static constexpr int count(int sg) {
+    return (sg + 1) * S <= ET ? S : ET - sg * S;
+  }
+  __host__ __device__ static constexpr int anchor(int sg) {
+    return first(sg) + count(sg) / 2;
+  }
+};
+
+// warp-uniform constants of one edge group for the current parameters
+template <int ET>
+struct GroupConst {
+  float cw[ET];     // w_e = cw[e] - kw*xc,  w = EB_HSCALE * zs
+  float kw;         // EB_HSCALE * ks
+  float ks;         // kappa / (sqrt2 sigma)
+  float csa;        // zs at the central edge = csa - ks*xc
+  float cs_lo, cs_hi;  // zs-scaled first / last edge of the group (skip test)
+  float two_d;      // 2 d,  d = ks * bin width
+  float nd2;        // -d^2
+  float kap;        // 2^(-2 d^2)
+  float csn[EbSeg<ET>::NSEG];  // zs-scaled anchor edge of every segment
+  float kup[EbSeg<ET>::NSEG];  // kap^(anchor - A0)
+  float kdn[EbSeg<ET>::NSEG];  // kap^(A0 - anchor)
+  float za_lim;     // recurrence allowed while |zs_A0| <= za_lim (<= 0: never)
+  const float* cs;  // shared memory: zs-scaled edges of the group (per-edge path)
+};
+
+// t, Horner polynomial and the four accumulations for up to CH consecutive
+// edges of a group starting at edge `base` (i < nvalid).
 //
-// The ET chains are written *stage by stage* (all edges do step i before any
-// edge does step i+1): ptxas keeps that order, so every warp always has ET
-// independent FFMA2 streams in flight and the 8-deep Horner recurrence never
-// exposes its latency (the chain-by-chain form ran at 62% FMA-pipe
-// utilisation with "wait" as the top stall reason; see profiles/).
-template <int ET, bool WEIGHTED>
-__device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
-                                           const float* __restrict__ cs,
-                                           float ks, float2 xc, float2 wt) {
-  float2 zs[ET], t[ET], g[ET], p[ET];
+// The chains of the chunk are written *stage by stage* (all edges do step i
+// before any edge does step i+1): ptxas keeps that order, so every warp has CH
+// independent FFMA2 streams in flight and the Horner recurrence never exposes
+// its latency.
+template <int CH, bool WEIGHTED>
+__device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
+                                         int nvalid, const float2* w,
+                                         const float2* g, float2 za,
+                                         float2 wt) {
+  float2 t[CH], p[CH];
 #pragma unroll
-  for (int e = 0; e < ET; ++e) zs[e] = vfma(xc, f2s(-ks), f2s(cs[e]));
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 d = vfma(f2(fabsf(zs[e].x), fabsf(zs[e].y)), f2s(EB_HSCALE),
-                          f2s(1.0f));
-    t[e] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
-  }
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 zz = vmul(zs[e], zs[e]);
-    g[e] = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
-  }
-  // Horner, stage by stage; coefficients pre-halved so that p = erfcx/2 / t
+  for (int i = 0; i < CH; ++i)
+    if (i < nvalid)
+      t[i] = f2(mgb_rcp(1.0f + fabsf(w[i].x)), mgb_rcp(1.0f + fabsf(w[i].y)));
+  // coefficients pre-halved so that p = erfcx/2 / t
   constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
-  for (int e = 0; e < ET; ++e)
-    p[e] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[e],
-                f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
+  for (int i = 0; i < CH; ++i)
+    if (i < nvalid)
+      p[i] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[i],
+                  f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
 #pragma unroll
   for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
 #pragma unroll
-    for (int e = 0; e < ET; ++e) p[e] = vfma(p[e], t[e], f2s(0.5f * kC[d]));
+    for (int i = 0; i < CH; ++i)
+      if (i < nvalid) p[i] = vfma(p[i], t[i], f2s(0.5f * kC[d]));
   }
 #pragma unroll
-  for (int e = 0; e < ET; ++e) p[e] = vmul(p[e], t[e]);
-  if (WEIGHTED) {
+  for (int i = 0; i < CH; ++i)
+    if (i < nvalid) p[i] = vmul(p[i], t[i]);
 #pragma unroll
-    for (int e = 0; e < ET; ++e) g[e] = vmul(g[e], wt);
-  }
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 q = vmul(p[e], g[e]);  // (w) * 1/2 erfc(|z|)
-    // ts = +q for z < 0, -q for z >= 0  (set the sign bit from ~sign(zs))
-    float2 ts;
-    ts.x = __uint_as_float(__float_as_uint(q.x) |
-                           (~__float_as_uint(zs[e].x) & 0x80000000u));
-    ts.y = __uint_as_float(__float_as_uint(q.y) |
-                           (~__float_as_uint(zs[e].y) & 0x80000000u));
-    a[e].T += ts.x;
-    a[e].T += ts.y;
-  }
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    if (WEIGHTED) {
-      a[e].O += zs[e].x >= 0.0f ? wt.x : 0.0f;
-      a[e].O += zs[e].y >= 0.0f ? wt.y : 0.0f;
-    } else {
-      // unweighted: count the objects *below* the edge on the integer pipe
-      // (sign bit of zs; the bit pattern of O is an int32 counter)
-      int c = __float_as_int(a[e].O);
-      c += (int)(__float_as_uint(zs[e].x) >> 31);
-      c += (int)(__float_as_uint(zs[e].y) >> 31);
-      a[e].O = __int_as_float(c);
+  for (int i = 0; i < CH; ++i) {
+    if (i < nvalid) {
+      EdgeAcc& ac = a[base + i];
+      // T += +q for z < 0, -q for z >= 0, q = p*g = (weight) 1/2 erfc(|z|):
+      // the sign goes onto g (sign bit from ~sign(w)), the product into the FMA
+      const float gx = __uint_as_float(
+          __float_as_uint(g[i].x) | (~__float_as_uint(w[i].x) & 0x80000000u));
+      const float gy = __uint_as_float(
+          __float_as_uint(g[i].y) | (~__float_as_uint(w[i].y) & 0x80000000u));
+      ac.T = fmaf(p[i].x, gx, ac.T);
+      ac.T = fmaf(p[i].y, gy, ac.T);
     }
   }
 #pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    a[e].G += g[e].x;
-    a[e].G += g[e].y;
-    a[e].Z = fmaf(zs[e].x, g[e].x, a[e].Z);
-    a[e].Z = fmaf(zs[e].y, g[e].y, a[e].Z);
+  for (int i = 0; i < CH; ++i) {
+    if (i < nvalid) {
+      EdgeAcc& ac = a[base + i];
+      if (WEIGHTED) {
+        ac.O += w[i].x >= 0.0f ? wt.x : 0.0f;
+        ac.O += w[i].y >= 0.0f ? wt.y : 0.0f;
+      } else {
+        // unweighted: count the objects *below* the edge on the integer pipe
+        // (sign bit of w; the bit pattern of O is an int32 counter)
+        int cnt = __float_as_int(ac.O);
+        cnt += (int)(__float_as_uint(w[i].x) >> 31);
+        cnt += (int)(__float_as_uint(w[i].y) >> 31);
+        ac.O = __int_as_float(cnt);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < CH; ++i) {
+    if (i < nvalid) {
+      EdgeAcc& ac = a[base + i];
+      ac.G += g[i].x;
+      ac.G += g[i].y;
+      ac.Z = fmaf(za.x, g[i].x, ac.Z);
+      ac.Z = fmaf(za.y, g[i].y, ac.Z);
+    }
+  }
+}
+
+// Gaussian of a pair at scaled coordinate zs = cs - ks*xc: g = 2^(-zs^2)
+template <bool WEIGHTED>
+__device__ __forceinline__ float2 eb_gauss(float2 xc, float ks, float cs,
+                                           float2 wt) {
+  const float2 zs = vfma(xc, f2s(-ks), f2s(cs));
+  const float2 zz = vmul(zs, zs);
+  float2 g = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
+  if (WEIGHTED) g = vmul(g, wt);
+  return g;
+}
+
+// Contribution of a pair of objects (centred coordinate xc, weight wt) to the
+// accumulators of the ET edges of a group, segment by segment.
+// CHAIN: only the anchor of a segment gets its Gaussian from MUFU.EX2; the
+// others follow by the recurrence
+//   upward    g_{e+1} = g_e rho_e,   rho_e = 2^(-2 zs_e d - d^2),
+//             rho_{e+1} = rho_e 2^(-2 d^2)
+//   downward  the same with d -> -d,
+// where rho at the first step of a segment is a per-object base ratio (one
+// MUFU.EX2 per direction, formed at the group's central edge A0) times a
+// per-segment constant.  At most EB_CHAIN_LEN ratios are multiplied up, which
+// bounds the accumulated relative error to about EB_CHAIN_LEN MUFU errors.
+template <int ET, bool WEIGHTED, bool CHAIN>
+__device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
+                                           const GroupConst<ET>& c, float2 xc,
+                                           float2 wt) {
+  typedef EbSeg<ET> SG;
+  constexpr int S = SG::S;
+  const float2 za = vfma(xc, f2s(-c.ks), f2s(c.csa));
+  float2 ru = f2s(0.f), rd = f2s(0.f);
+  if (CHAIN && S > 1) {
+    const float2 eu = vfma(za, f2s(-c.two_d), f2s(c.nd2));
+    ru = f2(mgb_ex2(eu.x), mgb_ex2(eu.y));
+    const float2 ed = vfma(za, f2s(c.two_d), f2s(c.nd2));
+    rd = f2(mgb_ex2(ed.x), mgb_ex2(ed.y));
+  }
+#pragma unroll
+  for (int sg = 0; sg < SG::NSEG; ++sg) {
+    const int e0 = SG::first(sg), n = SG::count(sg), an = SG::anchor(sg);
+    float2 w[S], g[S];
+#pragma unroll
+    for (int i = 0; i < S; ++i)
+      if (i < n) w[i] = vfma(xc, f2s(-c.kw), f2s(c.cw[e0 + i]));
+    if (CHAIN) {
+      const int ia = an - e0;
+      g[ia] = eb_gauss<WEIGHTED>(xc, c.ks, c.csn[sg], wt);
+      // ratio of the step an -> an+1 is ru * kap^(an - A0); of the step
+      // an -> an-1 it is rd * kap^(A0 - an)
+      if (ia + 1 < n) {
+        float2 r = vmul(ru, f2s(c.kup[sg]));
+        float2 gc = g[ia];
+#pragma unroll
+        for (int i = ia + 1; i < S; ++i) {
+          if (i < n) {
+            gc = vmul(gc, r);
+            g[i] = gc;
+            if (i + 1 < n) r = vmul(r, f2s(c.kap));
+          }
+        }
+      }
+      if (ia > 0) {
+        float2 r = vmul(rd, f2s(c.kdn[sg]));
+        float2 gc = g[ia];
+#pragma unroll
+        for (int i = ia - 1; i >= 0; --i) {
+          gc = vmul(gc, r);
+          g[i] = gc;
+          if (i > 0) r = vmul(r, f2s(c.kap));
+        }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < S; ++i)
+        if (i < n) g[i] = eb_gauss<WEIGHTED>(xc, c.ks, c.cs[e0 + i], wt);
+    }
+    eb_chunk<S, WEIGHTED>(a, e0, n, w, g, za, wt);
   }
 }
 
 // ---------------------------------------------------------------------------
 // Work decomposition.  The E = K+1 edges are split into NG groups of at most
 // EB_ET_MAX consecutive edges; a warp belongs to one group and only carries the
-// accumulators of that group's edges (8 registers per edge), which keeps the
-// kernel at <= 85 registers and 22-24 resident warps per SM.  Every group has
-// to see every object of the CTA, so a group with more edges gets
-// proportionally more warps (edge counts 6/5 -> 6 and 5 warps): all warps do
-// the same amount of work.  Per-edge sums are independent, so no edge is ever
-// evaluated twice; bin differences are taken after the CTA-level reduction.
+// accumulators of that group's edges.  Every group has to see every object of
+// the CTA, so a group with more edges gets proportionally more warps: all
+// warps do the same amount of work.  Per-edge sums are independent, so no edge
+// is ever evaluated twice; bin differences are taken after the CTA-level
+// reduction.
 // ---------------------------------------------------------------------------
 #ifndef EB_ET_MAX
-#define EB_ET_MAX 4
+#define EB_ET_MAX 11
 #endif
 #ifndef EB_MIN_CTAS
 #define EB_MIN_CTAS 2
@@ -184,88 +358,116 @@ __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
 #ifndef EB_TARGET_WARPS
 #define EB_TARGET_WARPS 24
 #endif
-#define EB_MAX_GROUPS ((MGB_MAX_BINS + 1 + EB_ET_MAX - 1) / EB_ET_MAX)
+#ifndef EB_MAX_WARPS
 #define EB_MAX_WARPS 12
+#endif
+#ifndef EB_WIDE_WARPS
+#define EB_WIDE_WARPS 8
+#endif
+// groups of more than EB_ET_NARROW edges run in CTAs of EB_WIDE_WARPS warps
+// compiled for 128 registers, the narrow ones in CTAs of up to EB_MAX_WARPS
+// warps at 80
+#ifndef EB_ET_NARROW
+#define EB_ET_NARROW 4
+#endif
+#define EB_MAX_GROUPS ((MGB_MAX_BINS + 1 + EB_ET_MAX - 1) / EB_ET_MAX)
 #define EB_MAX_EDGES (MGB_MAX_BINS + 1)
+#define EB_MAX_CLUSTER 8
+
+constexpr int eb_block_threads(int et_hi) {
+  return et_hi > EB_ET_NARROW ? EB_WIDE_WARPS * 32 : EB_MAX_WARPS * 32;
+}
+constexpr int eb_smem_warps() {
+  return EB_WIDE_WARPS > EB_MAX_WARPS ? EB_WIDE_WARPS : EB_MAX_WARPS;
+}
 
 struct EbLayout {
   int ng;                       // number of edge groups
   int nwarps;                   // warps per CTA
+  int uniform;                  // edges uniformly spaced (exactly, in fp64)
+  int pad_;
+  double width;                 // the common bin width when uniform
   int e0[EB_MAX_GROUPS + 1];    // first edge of group g (e0[ng] = E)
   int w0[EB_MAX_GROUPS + 1];    // first warp of group g (w0[ng] = nwarps)
 };
 
-// Accumulate the ET edges [e_first, e_first+ET) over the tiles of this CTA that
-// belong to warp `wj` of `wpg` warps in the group; leave the warp-reduced sums
-// (T, O, G, Z per edge) in s_out[4*ET] (lane 0 writes).
-template <int ET, bool WEIGHTED>
-__device__ __forceinline__ void accumulate_group(
-    const MgbErfBinModel& md, const float* __restrict__ cs_all, int e_first,
-    float ks, float x0, int wj, int wpg, int lane, double* s_out) {
-  float cs[ET];
-  EdgeAcc acc[ET];
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    cs[e] = cs_all[e_first + e];
-    acc[e].T = 0.f; acc[e].O = 0.f;
-    acc[e].G = 0.f; acc[e].Z = 0.f;
-  }
-  const float cs_lo = cs[0], cs_hi = cs[ET - 1];
+struct EbTile {
+  float4 x, w;
+};
+
+// one tile = 32 consecutive float4 (128 objects); lane `lane` of the warp
+// fetches its float4 (padding objects beyond the end)
+template <bool WEIGHTED>
+__device__ __forceinline__ void eb_fetch(const MgbErfBinModel& md,
+                                         long long base, int lane, EbTile& t) {
   const float4* __restrict__ x4 = reinterpret_cast<const float4*>(md.x);
   const float4* __restrict__ w4 = reinterpret_cast<const float4*>(md.w);
   const long long n4 = md.n >> 2;
-  // tile = 32 consecutive float4 (128 objects); CTA c owns tiles c, c+G, ...;
-  // within the CTA warp wj of the group takes every wpg-th of them.
-  const long long tstride = (long long)gridDim.x * wpg * 32;
-  long long i0 = ((long long)blockIdx.x + (long long)wj * gridDim.x) * 32;
-
-  auto fetch = [&](long long base, float4& xv, float4& wv) {
-    const long long i = base + lane;
-    if (i < n4) {
-      xv = __ldg(x4 + i);
-      if (WEIGHTED) wv = __ldg(w4 + i);
-    } else {
-      xv = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
-                       EB_SENTINEL_X);
-      if (WEIGHTED) wv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (i == n4) {  // ragged tail: the last n % 4 objects
-        const long long b4 = n4 << 2;
-        const int rem = (int)(md.n - b4);
-        if (rem > 0) xv.x = md.x[b4];
-        if (rem > 1) xv.y = md.x[b4 + 1];
-        if (rem > 2) xv.z = md.x[b4 + 2];
-        if (WEIGHTED) {
-          if (rem > 0) wv.x = md.w[b4];
-          if (rem > 1) wv.y = md.w[b4 + 1];
-          if (rem > 2) wv.z = md.w[b4 + 2];
-        }
+  const long long i = base + lane;
+  if (i < n4) {
+    t.x = __ldg(x4 + i);
+    if (WEIGHTED) t.w = __ldg(w4 + i);
+  } else {
+    t.x = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
+                      EB_SENTINEL_X);
+    if (WEIGHTED) t.w = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i == n4) {  // ragged tail: the last n % 4 objects
+      const long long b4 = n4 << 2;
+      const int rem = (int)(md.n - b4);
+      if (rem > 0) t.x.x = md.x[b4];
+      if (rem > 1) t.x.y = md.x[b4 + 1];
+      if (rem > 2) t.x.z = md.x[b4 + 2];
+      if (WEIGHTED) {
+        if (rem > 0) t.w.x = md.w[b4];
+        if (rem > 1) t.w.y = md.w[b4 + 1];
+        if (rem > 2) t.w.z = md.w[b4 + 2];
       }
     }
-  };
+  }
+}
 
-  float4 xn, wn = make_float4(1.f, 1.f, 1.f, 1.f);
-  if (i0 < n4 + 1) fetch(i0, xn, wn);
+// Accumulate the ET edges of a group over the tiles of this CTA that belong
+// to warp `wj` of `wpg` warps in the group; leave the warp-reduced sums
+// (T, O, G, Z' per edge) in s_out[4*ET] (lane 0 writes).  `first` holds the
+// warp's first tile, fetched by the caller (in the persistent fit before it
+// waits for the parameters of the step).
+template <int ET, bool WEIGHTED>
+__device__ __forceinline__ void accumulate_group(
+    const MgbErfBinModel& md, const GroupConst<ET>& c, float x0, int wj,
+    int wpg, int lane, const EbTile& first, double* s_out) {
+  EdgeAcc acc[ET];
+#pragma unroll
+  for (int e = 0; e < ET; ++e) {
+    acc[e].T = 0.f; acc[e].O = 0.f;
+    acc[e].G = 0.f; acc[e].Z = 0.f;
+  }
+  const long long n4 = md.n >> 2;
+  // CTA c owns tiles c, c+G, ...; within the CTA warp wj of the group takes
+  // every wpg-th of them.
+  const long long tstride = (long long)gridDim.x * wpg * 32;
+  long long i0 = ((long long)blockIdx.x + (long long)wj * gridDim.x) * 32;
+  EbTile nxt = first;
   // The trip count is warp-uniform (i0 does not depend on the lane) because the
   // body votes with __all_sync.  The next tile is fetched before the current
   // one is consumed (register double buffering hides the DRAM latency).
   for (; i0 < n4 + 1; i0 += tstride) {
-    const float4 xv = xn, wv = wn;
-    if (i0 + tstride < n4 + 1) fetch(i0 + tstride, xn, wn);
+    const float4 xv = nxt.x, wv = nxt.w;
+    if (i0 + tstride < n4 + 1) eb_fetch<WEIGHTED>(md, i0 + tstride, lane, nxt);
     const float2 xcA = vadd(f2(xv.x, xv.y), f2s(-x0));
     const float2 xcB = vadd(f2(xv.z, xv.w), f2s(-x0));
     // objects for which every edge of this group is saturated contribute
     // nothing to any difference between edges: skip them warp-uniformly
     const float cmin = fminf(fminf(xcA.x, xcA.y), fminf(xcB.x, xcB.y));
     const float cmax = fmaxf(fmaxf(xcA.x, xcA.y), fmaxf(xcB.x, xcB.y));
-    const bool far = (fmaf(-ks, cmax, cs_lo) > EB_ZS_SKIP) ||
-                     (fmaf(-ks, cmin, cs_hi) < -EB_ZS_SKIP);
+    const bool far = (fmaf(-c.ks, cmax, c.cs_lo) > EB_ZS_SKIP) ||
+                     (fmaf(-c.ks, cmin, c.cs_hi) < -EB_ZS_SKIP);
     if (__all_sync(0xffffffffu, far)) {
       // A skipped lane still has to keep the hard counts consistent with the
       // other edge groups, for which the same objects may not be saturated.
       if (WEIGHTED) {
         // O = weight of objects at or above the edge: all four objects of a
         // lane that is saturated on the high side (padding has weight 0)
-        if (fmaf(-ks, cmax, cs_lo) > EB_ZS_SKIP) {
+        if (fmaf(-c.ks, cmax, c.cs_lo) > EB_ZS_SKIP) {
           const float cnt = (wv.x + wv.y) + (wv.z + wv.w);
 #pragma unroll
           for (int e = 0; e < ET; ++e) acc[e].O += cnt;
@@ -274,7 +476,7 @@ __device__ __forceinline__ void accumulate_group(
         // O = number of objects below the edge: all four objects of a lane
         // saturated on the low side (padding objects sit there too, in every
         // group alike, so they cancel in the differences between edges)
-        if (fmaf(-ks, cmin, cs_hi) < -EB_ZS_SKIP) {
+        if (fmaf(-c.ks, cmin, c.cs_hi) < -EB_ZS_SKIP) {
 #pragma unroll
           for (int e = 0; e < ET; ++e)
             acc[e].O = __int_as_float(__float_as_int(acc[e].O) + 4);
@@ -282,8 +484,24 @@ __device__ __forceinline__ void accumulate_group(
       }
       continue;
     }
-    edges_pair<ET, WEIGHTED>(acc, cs, ks, xcA, f2(wv.x, wv.y));
-    edges_pair<ET, WEIGHTED>(acc, cs, ks, xcB, f2(wv.z, wv.w));
+    // the recurrence needs every object of the tile within za_lim of the
+    // central edge (in zs units); zs is monotone in xc
+    const bool near = fmaxf(fabsf(fmaf(-c.ks, cmax, c.csa)),
+                            fabsf(fmaf(-c.ks, cmin, c.csa))) <= c.za_lim;
+    // the two pairs of a lane go through the same code one after the other
+    // (not inlined twice: the wide kernels would not fit the instruction
+    // caches)
+    if (__all_sync(0xffffffffu, near)) {
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h)
+        edges_pair<ET, WEIGHTED, true>(acc, c, h ? xcB : xcA,
+                                       h ? f2(wv.z, wv.w) : f2(wv.x, wv.y));
+    } else {
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h)
+        edges_pair<ET, WEIGHTED, false>(acc, c, h ? xcB : xcA,
+                                        h ? f2(wv.z, wv.w) : f2(wv.x, wv.y));
+    }
   }
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
@@ -305,10 +523,65 @@ __device__ __forceinline__ void accumulate_group(
   }
 }
 
+// per-step shared state of a CTA
+struct EbShared {
+  float cs[EB_MAX_EDGES];              // zs-scaled centred edges
+  float cw[EB_MAX_EDGES];              // the same times EB_HSCALE (w units)
+  double dz[EB_MAX_EDGES];             // cs_e - cs_centre(e) in fp64
+  double warp[eb_smem_warps()][4 * EB_ET_MAX];
+  double edge[EB_MAX_EDGES][4];
+  double clu[EB_MAX_CLUSTER * 3 * MGB_MAX_BINS];  // leader: pushed partials
+  double tot[3 * MGB_MAX_BINS];
+  double stage[MGB_MAX_WORLD * 3 * MGB_MAX_BINS];
+  float pv[MGB_MAX_PARAMS];
+  unsigned tok;
+  int is_last;
+  int go;
+};
+
+template <int ET, bool WEIGHTED>
+__device__ __forceinline__ void run_group(const MgbErfBinModel& md,
+                                          EbShared& sh, double ks_d,
+                                          double width, bool uniform,
+                                          int e_first, int wj, int wpg,
+                                          int warp, int lane,
+                                          const EbTile& first) {
+  typedef EbSeg<ET> SG;
+  GroupConst<ET> c;
+  c.ks = (float)ks_d;
+  c.kw = (float)(ks_d * (double)EB_HSCALE);
+#pragma unroll
+  for (int e = 0; e < ET; ++e) c.cw[e] = sh.cw[e_first + e];
+  c.cs = sh.cs + e_first;
+  c.csa = sh.cs[e_first + SG::A0];
+  c.cs_lo = sh.cs[e_first];
+  c.cs_hi = sh.cs[e_first + ET - 1];
+  const double d = ks_d * width;
+  c.two_d = (float)(2.0 * d);
+  c.nd2 = (float)(-d * d);
+  c.kap = exp2f(-2.0f * (float)(d * d));
+#pragma unroll
+  for (int sg = 0; sg < SG::NSEG; ++sg) {
+    const float da = (float)(SG::anchor(sg) - SG::A0);
+    c.csn[sg] = sh.cs[e_first + SG::anchor(sg)];
+    c.kup[sg] = exp2f(-2.0f * (float)(d * d) * da);
+    c.kdn[sg] = exp2f(2.0f * (float)(d * d) * da);
+  }
+  c.za_lim = 0.f;
+  if (uniform && ET > 1) {
+    const double lim = (EB_CHAIN_EXP_MAX - (ET + 1) * d * d) / (2.0 * d);
+    c.za_lim = (float)(lim < (double)EB_ZA_MAX ? lim : (double)EB_ZA_MAX);
+  }
+  accumulate_group<ET, WEIGHTED>(md, c, md.x0, wj, wpg, lane, first,
+                                 sh.warp[warp]);
+}
+
 template <int ET_HI, bool WEIGHTED>
-__global__ void __launch_bounds__(EB_MAX_WARPS * 32, EB_MIN_CTAS)
-erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
-                   const MgbPeerTable pt, const EbLayout lay,
+__global__ void __launch_bounds__(eb_block_threads(ET_HI), EB_MIN_CTAS)
+erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
+                   const __grid_constant__ MgbStepArgs a,
+                   const __grid_constant__ MgbPeerTable pt,
+                   const __grid_constant__ EbLayout lay,
                    double* __restrict__ partials,
                    unsigned* __restrict__ counters) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -317,14 +590,22 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   const int G = gridDim.x;
   const int K = md.nbins;
   const int E = K + 1;
-  const int MP = 3 * K;  // doubles per CTA partial
+  const int MP = 3 * K;  // doubles per partial
+  const unsigned crank = eb_cluster_ctarank();
+  const unsigned csize = eb_cluster_nctarank();
+  const int NC = G / (int)csize;          // clusters = global partial rows
+  const int cid = blockIdx.x / (int)csize;
 
-  __shared__ float s_cs[EB_MAX_EDGES];
-  __shared__ double s_warp[EB_MAX_WARPS][4 * EB_ET_MAX];
-  __shared__ double s_edge[EB_MAX_EDGES][4];
-  __shared__ double s_tot[3 * MGB_MAX_BINS];
-  __shared__ double s_stage[MGB_MAX_WORLD * 3 * MGB_MAX_BINS];
-  __shared__ int s_is_last;
+  __shared__ EbShared sh;
+
+  // this warp's edge group
+  int grp = 0;
+  while (grp + 1 < lay.ng && warp >= lay.w0[grp + 1]) ++grp;
+  const int e_first = lay.e0[grp];
+  const int et = lay.e0[grp + 1] - e_first;
+  const int wpg = lay.w0[grp + 1] - lay.w0[grp];
+  const int wj = warp - lay.w0[grp];
+  const long long tile0 = ((long long)blockIdx.x + (long long)wj * G) * 32;
 
   // Programmatic dependent launch: this grid may have been scheduled while
   // the previous step's last CTA was still in its epilogue (launch latency and
@@ -335,6 +616,8 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   // gated launch: uniform early exit on every rank (no ticket, no exchange)
   if (a.gate != nullptr && __ldg(a.gate) == 0.0f) return;
 
+  const unsigned long long t_entry = a.trace ? mgb_globaltimer_ns() : 0ull;
+
   // pre-launched host-driven step: wait for the host to publish this step's
   // parameters.  Only CTA 0 talks to the host: a system-scope load of pinned
   // host memory is a PCIe round trip that is not merged with anybody else's
@@ -343,9 +626,8 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
   // device memory (spare words of the counter block), where the other CTAs
   // wait at L2 latency.  Relay token = wait_value (go) or wait_value with
   // bit 31 set (cancelled / timed out); the host zeroes it before a run.
-  __shared__ float s_pv[MGB_MAX_PARAMS];
+  bool have_params = false;
   if (a.wait_flag != nullptr) {
-    __shared__ unsigned s_tok;
     unsigned* relay_tok = counters + EB_RELAY_WORD;
     float* relay_pv = reinterpret_cast<float*>(counters + EB_RELAY_WORD + 8);
     const unsigned long long t0 = mgb_globaltimer_ns();
@@ -362,20 +644,20 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
           __nanosleep(EB_HOST_POLL_NS);
         }
         __threadfence_system();   // acquire: parameters written before flag
-        s_tok = tok;
+        sh.tok = tok;
       }
       __syncthreads();
-      if (!(s_tok & 0x80000000u) && tid < md.nparams) {
+      if (!(sh.tok & 0x80000000u) && tid < md.nparams) {
         const float v = __uint_as_float(mgb_ld_sys_u32(
             reinterpret_cast<const unsigned*>(a.params) + tid));
-        s_pv[tid] = v;
+        sh.pv[tid] = v;
         relay_pv[tid] = v;
       }
       __threadfence();
       __syncthreads();
       if (tid == 0)
         asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(relay_tok),
-                     "r"(s_tok) : "memory");
+                     "r"(sh.tok) : "memory");
     } else {
       if (tid == 0) {
         unsigned tok = a.wait_value | 0x80000000u;
@@ -387,178 +669,286 @@ erfbin_step_kernel(const MgbErfBinModel md, const MgbStepArgs a,
           if ((it & 63u) == 63u && mgb_globaltimer_ns() - t0 > 2 * limit) break;
         }
         __threadfence();
-        s_tok = tok;
+        sh.tok = tok;
       }
       __syncthreads();
-      if (!(s_tok & 0x80000000u) && tid < md.nparams)
-        s_pv[tid] = __ldcv(relay_pv + tid);
+      if (!(sh.tok & 0x80000000u) && tid < md.nparams)
+        sh.pv[tid] = __ldcv(relay_pv + tid);
     }
     __syncthreads();
-    if (s_tok & 0x80000000u) return;
-  } else {
+    if (sh.tok & 0x80000000u) return;
+    have_params = true;
+  }
+
+  // every CTA of the cluster is running from here on (its shared memory may be
+  // written by the others once this barrier has completed; the wait sits in
+  // front of the first remote store)
+  eb_cluster_arrive();
+  bool cluster_open = false;
+
+  const int nsteps = (a.mode >= MGB_MODE_ADAM && a.nsteps > 1) ? a.nsteps : 1;
+  const int step0 = (nsteps > 1) ? __ldcg(a.opt_step) : 0;
+
+  for (int s = 0; s < nsteps; ++s) {
+    // ---- first tile of the step: independent of the parameters, so it is in
+    // flight while this CTA waits for them ------------------------------------
+    EbTile first;
+    first.w = make_float4(1.f, 1.f, 1.f, 1.f);
+    if (tile0 < (md.n >> 2) + 1) eb_fetch<WEIGHTED>(md, tile0, lane, first);
+
+    if (s > 0) {
+      // persistent fit: wait until the elected CTA of the previous step has
+      // published the updated parameters (it bumps *opt_step last)
+      if (tid == 0) {
+        int go = 1;
+        const unsigned long long t0 = mgb_globaltimer_ns();
+        const unsigned long long limit =
+            2000000ull * (unsigned long long)(pt.world > 1
+                                                  ? pt.spin_timeout_ms
+                                                  : 20000u);
+        for (unsigned it = 0;; ++it) {
+          if (eb_ld_acquire_gpu_s32(a.opt_step) - step0 >= s) break;
+          if ((it & 63u) == 63u) {
+            if (__ldcv(counters + EB_ABORT_WORD) != 0u ||
+                mgb_globaltimer_ns() - t0 > limit) {
+              go = 0;
+              break;
+            }
+          }
+        }
+        sh.go = go;
+      }
+      __syncthreads();
+      if (!sh.go) break;
+    }
+    const unsigned long long t_start =
+        a.trace ? (s == 0 ? t_entry : mgb_globaltimer_ns()) : 0ull;
+
     // ---- parameters: one coalesced read per CTA (the vector may live in
-    // pinned host memory: zero-copy evaluation) ------------------------------
-    const float* pv = (a.mode >= MGB_MODE_ADAM)
-                          ? a.opt_p
-                          : (a.params + (size_t)b * md.nparams);
-    if (tid < md.nparams) s_pv[tid] = pv[tid];
+    // pinned host memory: zero-copy evaluation) --------------------------------
+    if (!have_params) {
+      const float* pv = (a.mode >= MGB_MODE_ADAM)
+                            ? a.opt_p
+                            : (a.params + (size_t)b * md.nparams);
+      if (tid < md.nparams)
+        sh.pv[tid] = (nsteps > 1) ? __ldcg(pv + tid) : pv[tid];
+      __syncthreads();
+    }
+    // ---- parameters -> scaled link constants ----------------------------------
+    const float p_mu = sh.pv[md.mu_idx];
+    const float p_sg = sh.pv[md.sig_idx];
+    const double sigma_d =
+        md.sigma_link == 1 ? exp10((double)p_sg) : (double)p_sg;
+    // Scaled, *centred* coordinates: with xc = x - x0 (exact in fp32 for data
+    // within a factor two of x0) and ks = kappa/(sqrt2 sigma),
+    //     zs_e = cs_e - ks*xc,   cs_e = (edge_e - p_mu - x0) * ks
+    // cs_e is formed in fp64 so that zs never subtracts two O(10) numbers.
+    const double ks_d = 1.2011224087864498 * 0.7071067811865476 / sigma_d;
+    if (tid < E) {
+      const double csd =
+          (md.edges[tid] - ((double)p_mu + (double)md.x0)) * ks_d;
+      sh.cs[tid] = (float)csd;
+      sh.cw[tid] = (float)(csd * (double)EB_HSCALE);
+      // offset of this edge from the central edge of its group (Z' -> Z)
+      int g2 = 0;
+      while (g2 + 1 < lay.ng && tid >= lay.e0[g2 + 1]) ++g2;
+      const int centre = lay.e0[g2] + (lay.e0[g2 + 1] - lay.e0[g2]) / 2;
+      sh.dz[tid] = (md.edges[tid] - md.edges[centre]) * ks_d;
+    }
     __syncthreads();
-  }
-  // ---- parameters -> scaled link constants --------------------------------
-  const float p_mu = s_pv[md.mu_idx];
-  const float p_sg = s_pv[md.sig_idx];
-  const double sigma_d =
-      md.sigma_link == 1 ? exp10((double)p_sg) : (double)p_sg;
-  // Scaled, *centred* coordinates: with xc = x - x0 (exact in fp32 for data
-  // within a factor two of x0) and ks = kappa/(sqrt2 sigma),
-  //     zs_e = cs_e - ks*xc,   cs_e = (edge_e - p_mu - x0) * ks
-  // cs_e is formed in fp64 so that zs never subtracts two O(10) numbers.
-  const double ks_d = 1.2011224087864498 * 0.7071067811865476 / sigma_d;
-  const float ks = (float)ks_d;
-  const float x0 = md.x0;
-  if (tid < E)
-    s_cs[tid] =
-        (float)(((double)md.edges[tid] - ((double)p_mu + (double)x0)) * ks_d);
-  __syncthreads();
 
-  // ---- main loop: this warp's edge group ------------------------------------
-  {
-    int g = 0;
-    while (g + 1 < lay.ng && warp >= lay.w0[g + 1]) ++g;
-    const int e_first = lay.e0[g];
-    const int et = lay.e0[g + 1] - e_first;
-    const int wpg = lay.w0[g + 1] - lay.w0[g];
-    const int wj = warp - lay.w0[g];
+    // ---- main loop: this warp's edge group -------------------------------------
     if (et == ET_HI) {
-      accumulate_group<ET_HI, WEIGHTED>(md, s_cs, e_first, ks, x0, wj, wpg,
-                                        lane, s_warp[warp]);
+      run_group<ET_HI, WEIGHTED>(md, sh, ks_d, lay.width, lay.uniform != 0,
+                                 e_first, wj, wpg, warp, lane, first);
     } else {
-      accumulate_group<(ET_HI > 1 ? ET_HI - 1 : 1), WEIGHTED>(
-          md, s_cs, e_first, ks, x0, wj, wpg, lane, s_warp[warp]);
+      run_group<(ET_HI > 1 ? ET_HI - 1 : 1), WEIGHTED>(
+          md, sh, ks_d, lay.width, lay.uniform != 0, e_first, wj, wpg, warp,
+          lane, first);
     }
-  }
-  // the object loop of this CTA is done: let the next step's grid be scheduled
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  __syncthreads();
-
-  // ---- CTA reduction in fp64: per-edge totals, then bin differences --------
-  for (int j = tid; j < 4 * E; j += nthreads) {
-    const int e = j >> 2, q = j & 3;
-    int g = 0;
-    while (g + 1 < lay.ng && e >= lay.e0[g + 1]) ++g;
-    double s = 0.0;
-    for (int w = lay.w0[g]; w < lay.w0[g + 1]; ++w)
-      s += s_warp[w][4 * (e - lay.e0[g]) + q];
-    s_edge[e][q] = s;
-  }
-  __syncthreads();
-  for (int j = tid; j < MP; j += nthreads) {
-    const int q = j / K, k = j - q * K;
-    double val;
-    if (q == 0) {
-      val = (s_edge[k + 1][1] - s_edge[k][1]) + (s_edge[k + 1][0] - s_edge[k][0]);
-    } else if (q == 1) {
-      val = s_edge[k + 1][2] - s_edge[k][2];
-    } else {
-      val = s_edge[k + 1][3] - s_edge[k][3];
+    // the object loop of this CTA is done: let the next launch's grid be
+    // scheduled
+    if (nsteps == 1)
+      asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (a.trace && tid == 0) {
+      unsigned long long* tr = reinterpret_cast<unsigned long long*>(a.trace) +
+                               (size_t)s * (8 + 2 * (size_t)G);
+      tr[8 + blockIdx.x] = t_start;
+      tr[8 + G + blockIdx.x] = mgb_globaltimer_ns();
     }
-    partials[((size_t)b * G + blockIdx.x) * MP + j] = val;
-  }
+    __syncthreads();
 
-  // ---- last-CTA election ---------------------------------------------------
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    const unsigned ticket = atomicAdd(&counters[b], 1u);
-    s_is_last = (ticket == (unsigned)(G - 1));
-  }
-  __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
-
-  // ---- fixed-order grid reduction ------------------------------------------
-  mgb_grid_reduce_f64(partials + (size_t)b * G * MP, G, MP, s_tot, tid,
-                      nthreads);
-  if (tid == 0) counters[b] = 0u;  // ready for the next launch
-  __syncthreads();
-
-  // ---- cross-GPU ordered all-reduce over NVLink ----------------------------
-  if (a.reduce && pt.world > 1) mgb_ll_allreduce_f64(pt, s_tot, s_stage, 3 * K);
-
-  // ---- epilogue (warp 0; lane k owns bin k) --------------------------------
-  if (warp != 0) return;
-  const double sig = sigma_d;
-  const double inv = 0.7071067811865476 / sig;             // 1/(sqrt2 sigma)
-  const double rsqrtpi = 0.5641895835477563;               // 1/sqrt(pi)
-  const double dsdp = md.sigma_link == 1 ? 2.302585092994046 * sig : 1.0;
-  const int P = md.nparams;
-  double s_k = 0.0, dmu_k = 0.0, dsg_k = 0.0;
-  if (lane < K) {
-    const double nrm = (double)md.norm[lane];
-    s_k = nrm * s_tot[lane];
-    dmu_k = -nrm * inv * rsqrtpi * s_tot[K + lane];
-    dsg_k = -nrm * (rsqrtpi * EB_INV_KAPPA / sig) * dsdp * s_tot[2 * K + lane];
-    if (a.out_sumstats) a.out_sumstats[(size_t)b * K + lane] = (float)s_k;
-    if (a.out_jac && a.mode >= MGB_MODE_SUMSTATS_JAC) {
-      float* jr = a.out_jac + ((size_t)b * K + lane) * P;
-      for (int i = 0; i < P; ++i) {
-        double v = 0.0;
-        if (i == md.mu_idx) v += dmu_k;
-        if (i == md.sig_idx) v += dsg_k;
-        jr[i] = (float)v;
+    // ---- CTA reduction in fp64: per-edge totals, then bin differences ---------
+    for (int j = tid; j < 4 * E; j += nthreads) {
+      const int e = j >> 2, q = j & 3;
+      int g2 = 0;
+      while (g2 + 1 < lay.ng && e >= lay.e0[g2 + 1]) ++g2;
+      double sum = 0.0;
+      for (int w = lay.w0[g2]; w < lay.w0[g2 + 1]; ++w)
+        sum += sh.warp[w][4 * (e - lay.e0[g2]) + q];
+      sh.edge[e][q] = sum;
+    }
+    __syncthreads();
+    // the first remote store of this launch needs every CTA of the cluster to
+    // have started
+    if (!cluster_open) {
+      eb_cluster_wait();
+      cluster_open = true;
+    }
+    {
+      const unsigned dst = eb_mapa(sh.clu, 0);
+      for (int j = tid; j < MP; j += nthreads) {
+        const int q = j / K, k = j - q * K;
+        double val;
+        if (q == 0) {
+          val = (sh.edge[k + 1][1] - sh.edge[k][1]) +
+                (sh.edge[k + 1][0] - sh.edge[k][0]);
+        } else if (q == 1) {
+          val = sh.edge[k + 1][2] - sh.edge[k][2];
+        } else {
+          // Z_e = Z'_e + (cs_e - cs_centre) G_e
+          val = (sh.edge[k + 1][3] + sh.dz[k + 1] * sh.edge[k + 1][2]) -
+                (sh.edge[k][3] + sh.dz[k] * sh.edge[k][2]);
+        }
+        eb_st_cluster_f64(dst + (unsigned)((crank * MP + j) * 8), val);
       }
     }
-  }
-  if (a.mode < MGB_MODE_LOSS_GRAD) return;
-
-  double l_k = 0.0, dl_k = 0.0;  // loss term and dL/ds_k
-  if (lane < K) {
-    const double tgt = (double)md.target[lane];
-    if (md.loss_kind == 0) {
-      const double eps = (double)md.loss_eps;
-      const double r = log10(s_k + eps) - log10(tgt + eps);
-      l_k = r * r / K;
-      dl_k = 2.0 * r / (K * (s_k + eps) * 2.302585092994046);
-    } else if (md.loss_kind == 1) {
-      const double r = s_k - tgt;
-      l_k = r * r / K;
-      dl_k = 2.0 * r / K;
-    } else {
-      const double ie = (double)md.inv_err[lane];
-      const double r = (s_k - tgt) * ie;
-      l_k = r * r;
-      dl_k = 2.0 * r * ie;
+    eb_cluster_arrive();
+    eb_cluster_wait();
+    bool last = false;
+    if (crank == 0) {
+      // leader: add the cluster's partials in rank order
+      for (int j = tid; j < MP; j += nthreads) {
+        double sum = 0.0;
+        for (unsigned r = 0; r < csize; ++r) sum += sh.clu[r * MP + j];
+        partials[((size_t)b * NC + cid) * MP + j] = sum;
+      }
+      // ---- last-leader election ------------------------------------------------
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) {
+        const unsigned ticket = atomicAdd(&counters[b], 1u);
+        sh.is_last = (ticket == (unsigned)(NC - 1));
+      }
+      __syncthreads();
+      last = sh.is_last != 0;
     }
-  }
-  const double loss = mgb_warp_sum(l_k);
-  const double gmu = mgb_warp_sum(dl_k * dmu_k);
-  const double gsg = mgb_warp_sum(dl_k * dsg_k);
-  // lane i owns parameter i from here on (the warp sums left loss / gmu / gsg
-  // in every lane): the optimiser-state loads of all parameters are then in
-  // flight together instead of one dependent L2 round trip after another
-  const int i = lane;
-  const bool mine = i < P;
-  float grad = 0.f;
-  if (mine) {
-    double v = 0.0;
-    if (i == md.mu_idx) v += gmu;
-    if (i == md.sig_idx) v += gsg;
-    grad = (float)v;
-  }
-  if (lane == 0 && a.out_loss) a.out_loss[b] = (float)loss;
-  if (mine && a.out_grad) a.out_grad[(size_t)b * P + i] = grad;
-  if (a.mode < MGB_MODE_ADAM) return;
+    if (!last) continue;   // next step (or exit): wait for the elected CTA
+    __threadfence();
+    unsigned long long tr1 = 0, tr2 = 0, tr3 = 0;
+    if (a.trace && tid == 0) tr1 = mgb_globaltimer_ns();
 
-  // ---- optimiser update (replicated, deterministic on every GPU) ----------
-  const int step = *a.opt_step;       // updates applied so far (bias corr.)
-  const int row = step - a.step_base;  // row of this step in the buffers
-  if (lane == 0 && a.loss_hist && row >= 0 && row < a.traj_rows)
-    a.loss_hist[row] = (float)loss;
-  if (mine)
-    mgb_opt_update_param(a, i, P, step, row, grad, a.bound_kind[i],
-                         a.bound_lo[i], a.bound_hi[i]);
-  __syncwarp();                       // every lane has read the step counter
-  if (lane == 0) *a.opt_step = step + 1;
+    // ---- fixed-order grid reduction --------------------------------------------
+    mgb_grid_reduce_f64(partials + (size_t)b * NC * MP, NC, MP, sh.tot, tid,
+                        nthreads);
+    if (tid == 0) counters[b] = 0u;  // ready for the next step / launch
+    __syncthreads();
+    if (a.trace && tid == 0) tr2 = mgb_globaltimer_ns();
+
+    // ---- cross-GPU ordered all-reduce over NVLink ------------------------------
+    if (a.reduce && pt.world > 1)
+      mgb_ll_allreduce_f64(pt, sh.tot, sh.stage, 3 * K);
+    if (a.trace && tid == 0) tr3 = mgb_globaltimer_ns();
+
+    // ---- epilogue (warp 0; lane k owns bin k) ----------------------------------
+    if (warp == 0) {
+      const double sig = sigma_d;
+      const double inv = 0.7071067811865476 / sig;           // 1/(sqrt2 sigma)
+      const double rsqrtpi = 0.5641895835477563;             // 1/sqrt(pi)
+      const double dsdp = md.sigma_link == 1 ? 2.302585092994046 * sig : 1.0;
+      const int P = md.nparams;
+      double s_k = 0.0, dmu_k = 0.0, dsg_k = 0.0;
+      if (lane < K) {
+        const double nrm = (double)md.norm[lane];
+        s_k = nrm * sh.tot[lane];
+        dmu_k = -nrm * inv * rsqrtpi * sh.tot[K + lane];
+        dsg_k =
+            -nrm * (rsqrtpi * EB_INV_KAPPA / sig) * dsdp * sh.tot[2 * K + lane];
+        if (a.out_sumstats) a.out_sumstats[(size_t)b * K + lane] = (float)s_k;
+        if (a.out_jac && a.mode >= MGB_MODE_SUMSTATS_JAC) {
+          float* jr = a.out_jac + ((size_t)b * K + lane) * P;
+          for (int i = 0; i < P; ++i) {
+            double v = 0.0;
+            if (i == md.mu_idx) v += dmu_k;
+            if (i == md.sig_idx) v += dsg_k;
+            jr[i] = (float)v;
+          }
+        }
+      }
+      if (a.mode >= MGB_MODE_LOSS_GRAD) {
+        double l_k = 0.0, dl_k = 0.0;  // loss term and dL/ds_k
+        if (lane < K) {
+          const double tgt = (double)md.target[lane];
+          if (md.loss_kind == 0) {
+            const double eps = (double)md.loss_eps;
+            const double r = log10(s_k + eps) - log10(tgt + eps);
+            l_k = r * r / K;
+            dl_k = 2.0 * r / (K * (s_k + eps) * 2.302585092994046);
+          } else if (md.loss_kind == 1) {
+            const double r = s_k - tgt;
+            l_k = r * r / K;
+            dl_k = 2.0 * r / K;
+          } else {
+            const double ie = (double)md.inv_err[lane];
+            const double r = (s_k - tgt) * ie;
+            l_k = r * r;
+            dl_k = 2.0 * r * ie;
+          }
+        }
+        const double loss = mgb_warp_sum(l_k);
+        const double gmu = mgb_warp_sum(dl_k * dmu_k);
+        const double gsg = mgb_warp_sum(dl_k * dsg_k);
+        // lane i owns parameter i from here on (the warp sums left loss / gmu
+        // / gsg in every lane): the optimiser-state loads of all parameters
+        // are then in flight together
+        const int i = lane;
+        const bool mine = i < P;
+        float grad = 0.f;
+        if (mine) {
+          double v = 0.0;
+          if (i == md.mu_idx) v += gmu;
+          if (i == md.sig_idx) v += gsg;
+          grad = (float)v;
+        }
+        if (lane == 0 && a.out_loss) a.out_loss[b] = (float)loss;
+        if (mine && a.out_grad) a.out_grad[(size_t)b * P + i] = grad;
+        if (a.mode >= MGB_MODE_ADAM) {
+          // ---- optimiser update (replicated, deterministic on every GPU) ----
+          const int step = __ldcg(a.opt_step);  // updates applied so far
+          const int row = step - a.step_base;   // row of this step
+          if (lane == 0 && a.loss_hist && row >= 0 && row < a.traj_rows)
+            a.loss_hist[row] = (float)loss;
+          if (mine)
+            mgb_opt_update_param(a, i, P, step, row, grad, a.bound_kind[i],
+                                 a.bound_lo[i], a.bound_hi[i]);
+          __syncwarp();                   // every lane has written its state
+          if (lane == 0) {
+            if (nsteps > 1) {
+              // a failed exchange poisons the state: stop the fit everywhere
+              if (pt.world > 1 &&
+                  mgb_ld_sys_u32(mgb_ctrl(pt, pt.rank) + MGB_CTRL_ERROR) != 0u)
+                counters[EB_ABORT_WORD] = 1u;
+              __threadfence();
+              eb_st_release_gpu_s32(a.opt_step, step + 1);
+            } else {
+              *a.opt_step = step + 1;
+            }
+          }
+        }
+      }
+    }
+    if (a.trace && tid == 0) {
+      unsigned long long* tr = reinterpret_cast<unsigned long long*>(a.trace) +
+                               (size_t)s * (8 + 2 * (size_t)G);
+      tr[0] = t_start;
+      tr[1] = tr1;
+      tr[2] = tr2;
+      tr[3] = tr3;
+      tr[4] = mgb_globaltimer_ns();
+      tr[5] = (unsigned long long)blockIdx.x;
+    }
+    if (nsteps > 1) __syncthreads();
+  }
 }
 
 typedef void (*eb_kernel_t)(const MgbErfBinModel, const MgbStepArgs,
@@ -578,32 +968,63 @@ eb_kernel_t pick_kernel(int et_hi) {
 #if EB_ET_MAX >= 6
     case 6: return erfbin_step_kernel<6, W>;
 #endif
+#if EB_ET_MAX >= 7
+    case 7: return erfbin_step_kernel<7, W>;
+#endif
+#if EB_ET_MAX >= 8
+    case 8: return erfbin_step_kernel<8, W>;
+#endif
+#if EB_ET_MAX >= 9
+    case 9: return erfbin_step_kernel<9, W>;
+#endif
+#if EB_ET_MAX >= 10
+    case 10: return erfbin_step_kernel<10, W>;
+#endif
+#if EB_ET_MAX >= 11
+    case 11: return erfbin_step_kernel<11, W>;
+#endif
   }
   return nullptr;
 }
 
 // Edge groups and warps per group for K bins (see the comment above EbLayout).
-EbLayout make_layout(int nbins, int* et_hi_out) {
+EbLayout make_layout(const MgbErfBinModel& md, int* et_hi_out) {
   EbLayout L;
+  memset(&L, 0, sizeof(L));
+  const int nbins = md.nbins;
   const int E = nbins + 1;
   L.ng = (E + EB_ET_MAX - 1) / EB_ET_MAX;
   const int lo = E / L.ng, extra = E % L.ng;  // `extra` groups get lo+1 edges
   const int et_hi = lo + (extra ? 1 : 0);
+  const int maxw = eb_block_threads(et_hi) / 32;
   // Warps per group: proportional to the group's edge count while one warp
   // per edge fits in a CTA (perfect balance), else the same number of warps
-  // for every group (a 3-edge group then idles 25% of the time).
-  const int even = EB_MAX_WARPS / L.ng > 0 ? EB_MAX_WARPS / L.ng : 1;
+  // for every group; a single group takes the whole CTA.
+  const int even = maxw / L.ng > 0 ? maxw / L.ng : 1;
   int e = 0, w = 0;
   for (int g = 0; g < L.ng; ++g) {
     const int et = lo + (g < extra ? 1 : 0);
     L.e0[g] = e;
     L.w0[g] = w;
     e += et;
-    w += (E <= EB_MAX_WARPS) ? et : even;
+    w += (L.ng == 1) ? maxw : ((E <= maxw) ? et : even);
   }
   L.e0[L.ng] = e;
   L.w0[L.ng] = w;
   L.nwarps = w;
+  // exactly uniform spacing (to fp64 rounding), as produced by linspace
+  const double width = (md.edges[nbins] - md.edges[0]) / nbins;
+  bool uni = width > 0.0;
+  for (int k = 0; k <= nbins && uni; ++k) {
+    const double want = md.edges[0] + k * width;
+    const double tol = 8.0 * 2.220446049250313e-16 *
+                       (fabs(md.edges[0]) + fabs(md.edges[nbins]) + width);
+    uni = fabs(md.edges[k] - want) <= tol;
+  }
+  const char* env = getenv("MULTIGRAD_B200_CHAIN");
+  if (env && env[0] == '0') uni = false;
+  L.uniform = uni ? 1 : 0;
+  L.width = width;
   *et_hi_out = et_hi;
   return L;
 }
@@ -622,17 +1043,108 @@ int sm_count() {
   return sms;
 }
 
-// CTAs per SM so that about 24 warps are resident
+// CTAs per SM so that about EB_TARGET_WARPS warps are resident (the wide
+// kernels are compiled for EB_MIN_CTAS CTAs of 128 registers)
 int grid_for(int nbins) {
-  int et_hi;
-  const EbLayout L = make_layout(nbins, &et_hi);
-  int per_sm = EB_TARGET_WARPS / L.nwarps;
+  MgbErfBinModel tmp;
+  memset(&tmp, 0, sizeof(tmp));
+  tmp.nbins = nbins;
+  int et_hi = 0;
+  const int nwarps = make_layout(tmp, &et_hi).nwarps;
+  int per_sm = EB_TARGET_WARPS / nwarps;
+  const int cap = et_hi > EB_ET_NARROW ? EB_MIN_CTAS : 8;
   if (per_sm < 1) per_sm = 1;
-  if (per_sm > 8) per_sm = 8;
+  if (per_sm > cap) per_sm = cap;
   return sm_count() * per_sm;
 }
 
+// Thread-block cluster size wanted: MULTIGRAD_B200_CLUSTER (1, 2, 4 or 8;
+// default 4), reduced until it divides the grid.
+int cluster_for(int grid) {
+  int c = 4;
+  const char* env = getenv("MULTIGRAD_B200_CLUSTER");
+  if (env && env[0]) c = atoi(env);
+  if (c != 1 && c != 2 && c != 4 && c != 8) c = 4;
+  while (c > 1 && grid % c) c >>= 1;
+  return c;
+}
+
+// Largest cluster size <= the wanted one with which a whole wave of the grid
+// (grid CTAs) is resident at once: a cluster is placed as a unit, so too
+// large a cluster leaves SMs idle (measured: clusters of 4 with two
+// 128-register CTAs per SM run the grid in 1.5 waves).  The answer is cached
+// per kernel, device and launch shape.
+struct EbClusterChoice {
+  const void* fn;
+  int dev, grid, block, want, csize;
+};
+EbClusterChoice g_cluster_cache[32];
+int g_cluster_cached = 0;
+std::mutex g_cluster_mutex;
+
+int pick_cluster(eb_kernel_t k, int grid, int block, int* out) {
+  int dev = 0;
+  MGB_CUDA_CHECK(cudaGetDevice(&dev));
+  const int want = cluster_for(grid);
+  std::lock_guard<std::mutex> lock(g_cluster_mutex);
+  for (int i = 0; i < g_cluster_cached; ++i) {
+    const EbClusterChoice& c = g_cluster_cache[i];
+    if (c.fn == (const void*)k && c.dev == dev && c.grid == grid &&
+        c.block == block && c.want == want) {
+      *out = c.csize;
+      return MGB_OK;
+    }
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3((unsigned)block, 1, 1);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int csize = want;
+  for (; csize > 1; csize >>= 1) {
+    attr[0].val.clusterDim.x = (unsigned)csize;
+    int max_clusters = 0;
+    const cudaError_t e =
+        cudaOccupancyMaxActiveClusters(&max_clusters, k, &cfg);
+    if (e == cudaSuccess && max_clusters * csize >= grid) break;
+    if (e != cudaSuccess) (void)cudaGetLastError();
+  }
+  if (g_cluster_cached < 32) {
+    EbClusterChoice& c = g_cluster_cache[g_cluster_cached++];
+    c.fn = (const void*)k;
+    c.dev = dev;
+    c.grid = grid;
+    c.block = block;
+    c.want = want;
+    c.csize = csize;
+  }
+  *out = csize;
+  return MGB_OK;
+}
+
 }  // namespace
+
+// cluster size the fused step will be launched with (diagnostics)
+extern "C" int mgb_erfbin_cluster(int nbins, int weighted) {
+  if (nbins < 1 || nbins > MGB_MAX_BINS) return 0;
+  MgbErfBinModel tmp;
+  memset(&tmp, 0, sizeof(tmp));
+  tmp.nbins = nbins;
+  int et_hi = 0;
+  const EbLayout lay = make_layout(tmp, &et_hi);
+  eb_kernel_t k =
+      weighted ? pick_kernel<true>(et_hi) : pick_kernel<false>(et_hi);
+  int csize = 0;
+  if (!k ||
+      pick_cluster(k, grid_for(nbins), lay.nwarps * 32, &csize) != MGB_OK)
+    return 0;
+  return csize;
+}
 
 extern "C" int mgb_erfbin_grid(int nbins) {
   if (nbins < 1 || nbins > MGB_MAX_BINS) return 0;
@@ -667,6 +1179,9 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
               "mgb_erfbin_step: x is null");
   MGB_REQUIRE(((uintptr_t)md.x & 15u) == 0 && ((uintptr_t)md.w & 15u) == 0,
               MGB_EINVAL, "mgb_erfbin_step: x / w must be 16-byte aligned");
+  for (int k = 0; k < md.nbins; ++k)
+    MGB_REQUIRE(md.edges[k + 1] > md.edges[k], MGB_EINVAL,
+                "mgb_erfbin_step: bin edges must be strictly increasing");
   MGB_REQUIRE(a.batch >= 1 && a.batch <= MGB_MAX_BATCH, MGB_ETOOBIG,
               "mgb_erfbin_step: batch=%d outside [1,%d]", a.batch,
               MGB_MAX_BATCH);
@@ -684,6 +1199,12 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
     MGB_REQUIRE(a.params != nullptr, MGB_EINVAL,
                 "mgb_erfbin_step: params is null");
   }
+  const bool persistent = a.nsteps > 1;
+  MGB_REQUIRE(!persistent || (a.mode >= MGB_MODE_ADAM && !a.gate &&
+                              !a.wait_flag),
+              MGB_EINVAL,
+              "mgb_erfbin_step: nsteps > 1 needs an optimiser mode and "
+              "neither gate nor host hand-shake");
   MgbPeerTable ptv;
   if (pt) {
     ptv = *pt;
@@ -699,7 +1220,7 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
                 MGB_ETOOBIG, "mgb_erfbin_step: peer table too small");
   }
   int et_hi = 0;
-  const EbLayout lay = make_layout(md.nbins, &et_hi);
+  const EbLayout lay = make_layout(md, &et_hi);
   const int grid = grid_for(md.nbins);
   MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_erfbin_step: no CUDA device");
   MGB_REQUIRE(a.wait_flag == nullptr ||
@@ -725,11 +1246,32 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   cfg.blockDim = blk;
   cfg.dynamicSmemBytes = 0;
   cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  int csize = 1;
+  {
+    const int rc = pick_cluster(k, grid, (int)blk.x, &csize);
+    if (rc != MGB_OK) return rc;
+  }
+  cudaLaunchAttribute attr[3];
+  int na = 0;
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = (unsigned)csize;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  if (persistent) {
+    // every CTA of the grid has to be resident at once (pick_cluster checked
+    // that it can be); the cooperative attribute makes the driver refuse the
+    // launch instead of deadlocking if it cannot
+    attr[na].id = cudaLaunchAttributeCooperative;
+    attr[na].val.cooperative = 1;
+    ++na;
+  } else {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = na;
   MGB_CUDA_CHECK(
       cudaLaunchKernelEx(&cfg, k, md, a, ptv, lay, partials, counters));
   return MGB_OK;

@@ -136,7 +136,9 @@ typedef struct MgbErfBinModel {
   float x0;              /* centring constant: the kernel works on x - x0;
                             pick a value near the bulk of the data (any value
                             is valid, 0 disables centring)                  */
-  float edges[MGB_MAX_BINS + 1];
+  double edges[MGB_MAX_BINS + 1]; /* fp64: the scaled edge constants are
+                            formed in double, and exactly uniform spacing (as
+                            from linspace) enables the Gaussian recurrence    */
   float norm[MGB_MAX_BINS];    /* s_k = norm_k * sum_h (Phi_{k+1}-Phi_k)     */
   float target[MGB_MAX_BINS];
   float inv_err[MGB_MAX_BINS];
@@ -185,11 +187,24 @@ typedef struct MgbStepArgs {
   const uint32_t* wait_flag;
   uint32_t wait_value;
   uint32_t wait_timeout_ms;
+  /* Persistent fit (modes 3/4): nsteps > 1 runs that many optimiser steps in
+   * ONE launch (all CTAs co-resident; between steps they wait on the device
+   * for the elected CTA that reduces, exchanges over NVLink and updates the
+   * parameters) -- the analogue of the reference's collectives inside one
+   * compiled lax.scan (multigrad/mpi4jax/multigrad.py:38-58).  0 or 1: one
+   * step per launch. */
+  int32_t nsteps;
+  int32_t reserved0;
+  /* Optional device buffer of %globaltimer stamps (tools/step_trace.py):
+   * per step 8 + 2*grid uint64 words; NULL = no tracing. */
+  uint64_t* trace;
 } MgbStepArgs;
 
 /* scratch needed by mgb_erfbin_step: bytes for `scratch` given the batch */
 uint64_t mgb_erfbin_scratch_bytes(int nbins, int batch);
 int mgb_erfbin_grid(int nbins);
+/* thread-block cluster size the fused step is launched with (diagnostics) */
+int mgb_erfbin_cluster(int nbins, int weighted);
 /* `scratch` must be zero-filled once before its first use. */
 int mgb_erfbin_step(const MgbErfBinModel* model, const MgbStepArgs* args,
                     const MgbPeerTable* pt, void* scratch,

@@ -101,7 +101,7 @@ class ErfBinnedModel(OnePointModel):
         self._edges64 = _np(self.bin_edges).ravel()
         self.nbins = self._edges64.size - 1
         self._norm64 = 1.0 / (float(self.volume) * np.diff(self._edges64))
-        self._edges_t = torch.as_tensor(self._edges64, dtype=torch.float32,
+        self._edges_t = torch.as_tensor(self._edges64, dtype=torch.float64,
                                         device=self.device)
         self._norm_t = torch.as_tensor(self._norm64, dtype=torch.float32,
                                        device=self.device)
@@ -456,11 +456,29 @@ class ErfBinnedModel(OnePointModel):
                                  aux=[None] * nsteps)
 
     def _run_steps(self, plan, args, nsteps: int, use_graph) -> None:
-        """Issue ``nsteps`` fused step launches, optionally as replays of a
-        captured CUDA graph (the step index and the collective epoch live on
-        the device, so a replay is a valid continuation)."""
+        """Run ``nsteps`` optimiser steps.  Default: *persistent* launches --
+        up to ``MULTIGRAD_B200_PERSISTENT_CHUNK`` (4096) steps inside ONE
+        kernel, whose CTAs stay resident and hand the parameters on through
+        device memory (the step index and the collective epoch live on the
+        device, so consecutive launches continue each other).  With
+        ``MULTIGRAD_B200_PERSISTENT=0`` or ``use_graph`` one launch per step,
+        optionally as replays of a captured CUDA graph.  The trajectories of
+        all three forms are bit-identical."""
+        persistent = os.environ.get("MULTIGRAD_B200_PERSISTENT", "1") != "0"
         if use_graph is None:
             use_graph = os.environ.get("MULTIGRAD_B200_GRAPH", "0") == "1"
+        if persistent and not use_graph and nsteps > 1:
+            chunk = int(os.environ.get("MULTIGRAD_B200_PERSISTENT_CHUNK",
+                                       "4096"))
+            done = 0
+            while done < nsteps:
+                n = min(chunk, nsteps - done)
+                args.nsteps = n
+                plan.launch(args)
+                done += n
+            args.nsteps = 1
+            return
+        args.nsteps = 1
         chunk = int(os.environ.get("MULTIGRAD_B200_GRAPH_CHUNK", "50"))
         done = 0
         if use_graph and nsteps >= 2 * chunk:

@@ -59,7 +59,7 @@ class MgbErfBinModel(C.Structure):
         ("mu_idx", C.c_int32), ("sig_idx", C.c_int32),
         ("sigma_link", C.c_int32), ("loss_kind", C.c_int32),
         ("loss_eps", C.c_float), ("x0", C.c_float),
-        ("edges", C.c_float * (MGB_MAX_BINS + 1)),
+        ("edges", C.c_double * (MGB_MAX_BINS + 1)),
         ("norm", C.c_float * MGB_MAX_BINS),
         ("target", C.c_float * MGB_MAX_BINS),
         ("inv_err", C.c_float * MGB_MAX_BINS),
@@ -85,6 +85,8 @@ class MgbStepArgs(C.Structure):
         ("bound_hi", C.c_float * MGB_MAX_PARAMS),
         ("wait_flag", C.c_void_p), ("wait_value", C.c_uint32),
         ("wait_timeout_ms", C.c_uint32),
+        ("nsteps", C.c_int32), ("reserved0", C.c_int32),
+        ("trace", C.c_void_p),
     ]
 
 
@@ -206,6 +208,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.mgb_erfbin_scratch_bytes.argtypes = [C.c_int, C.c_int]
     lib.mgb_erfbin_grid.restype = C.c_int
     lib.mgb_erfbin_grid.argtypes = [C.c_int]
+    lib.mgb_erfbin_cluster.restype = C.c_int
+    lib.mgb_erfbin_cluster.argtypes = [C.c_int, C.c_int]
     lib.mgb_erfbin_step.argtypes = [C.POINTER(MgbErfBinModel),
                                     C.POINTER(MgbStepArgs),
                                     C.POINTER(MgbPeerTable), vp, u64, vp]

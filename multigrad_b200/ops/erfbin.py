@@ -147,18 +147,19 @@ class ErfBinPlan:
         single = p.dim() == 1
         p = p.reshape(-1, self.P).contiguous()
         B = p.shape[0]
-        out = {"sumstats": torch.empty(B, self.K, device=self.device)}
+        f32 = dict(dtype=torch.float32, device=self.device)
+        out = {"sumstats": torch.empty(B, self.K, **f32)}
         a = MgbStepArgs()
         a.mode, a.batch = mode, B
         a.reduce = 1 if (reduce and self.world > 1) else 0
         a.params = p.data_ptr()
         a.out_sumstats = out["sumstats"].data_ptr()
         if mode >= MODE_SUMSTATS_JAC:
-            out["jac"] = torch.empty(B, self.K, self.P, device=self.device)
+            out["jac"] = torch.empty(B, self.K, self.P, **f32)
             a.out_jac = out["jac"].data_ptr()
         if mode >= MODE_LOSS_GRAD:
-            out["loss"] = torch.empty(B, device=self.device)
-            out["grad"] = torch.empty(B, self.P, device=self.device)
+            out["loss"] = torch.empty(B, **f32)
+            out["grad"] = torch.empty(B, self.P, **f32)
             a.out_loss = out["loss"].data_ptr()
             a.out_grad = out["grad"].data_ptr()
         self.launch(a)
@@ -173,9 +174,14 @@ class ErfBinPlan:
     def make_optimizer_args(self, mode: int, state: "FitState", lr: float,
                             bounds: Optional[Sequence] = None,
                             jac_at_params: bool = True, b1=0.9, b2=0.999,
-                            eps=1e-8, outputs: bool = False) -> MgbStepArgs:
+                            eps=1e-8, outputs: bool = False,
+                            nsteps: int = 1) -> MgbStepArgs:
+        """Argument block of an optimiser launch.  ``nsteps > 1`` makes it a
+        *persistent* launch: that many steps inside one kernel (see
+        ``MgbStepArgs.nsteps`` in ``include/multigrad_b200.h``)."""
         a = MgbStepArgs()
         a.mode, a.batch = mode, 1
+        a.nsteps = int(nsteps)
         a.reduce = 1 if self.world > 1 else 0
         a.jac_at_params = 1 if jac_at_params else 0
         a.opt_p, a.opt_u = state.p.data_ptr(), state.u.data_ptr()

@@ -24,7 +24,7 @@ def dev():
 def oracle(x, edges, norm, p, link="identity", weights=None):
     """float64 (s, ds/dmu, ds/dsig) on the float32 inputs."""
     x64 = x.double().cpu()
-    e64 = torch.as_tensor(np.asarray(edges, dtype=np.float32)).double()
+    e64 = torch.as_tensor(np.asarray(edges, dtype=np.float64))
     n64 = torch.as_tensor(np.asarray(norm, dtype=np.float32)).double()
     w64 = None if weights is None else weights.double().cpu()
     p64 = torch.as_tensor(np.asarray(p, dtype=np.float32)).double()
