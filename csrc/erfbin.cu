@@ -9,15 +9,15 @@
 //                   g   = 2^(-zs^2) = exp(-z^2)
 //                   q   = 1/2 erfc(|z|) = g * t*P(t)/2, t = 1/(1+|z|/2) (MUFU.RCP)
 //               and accumulates per edge  T = sum -+q (tail part of the CDF),
-//               O = sum [z>=0] (hard count), G = sum g, Z' = sum zs_centre*g.
+//               O = sum [z>=0] (hard count), G = sum g, Z = sum zs*g.
 //               Phi = O + T exactly, so bin sums never subtract numbers near 1.
-//               Uniformly spaced edges: only every (2L+1)-th edge (an anchor)
-//               gets its Gaussian from MUFU.EX2; its neighbours follow by a
+//               Uniformly spaced edges: only the central edge of a group gets
+//               its Gaussian from MUFU.EX2; the others follow by a
 //               multiplicative recurrence
 //                   g_{e+1} = g_e * rho_e,   rho_{e+1} = rho_e * 2^(-2 d^2)
-//               Tiles with an object too far from the group's central edge
-//               for that to be accurate, and non-uniform edges, take the
-//               per-edge MUFU.EX2 path.
+//               Tiles with an object too far from the central edge for that
+//               to be accurate, and non-uniform edges, take the per-edge
+//               MUFU.EX2 path.
 //   CTA reduce  warp shuffles in fp32, cross-warp and everything after in fp64.
 //   cluster     the CTAs of a thread-block cluster push their 3K partial sums
 //               into the leader CTA's shared memory (DSMEM, st.shared::cluster)
@@ -88,17 +88,17 @@ __device__ __forceinline__ float2 vfma(float2 a, float2 b, float2 c) {
 // kappa = sqrt(log2(e)): exp(-z^2) == 2^(-(kappa z)^2)
 #define EB_KAPPA 1.2011224087864498f
 #define EB_INV_KAPPA 0.8325546111576977
-// t = 1/(1 + c |z|) = 1/(1 + |w|), w = (c/kappa) zs, c = MGB_ERFCX_CSCALE
+// t = 1/(1 + c |z|) = 1/(1 + (c/kappa) |zs|), c = MGB_ERFCX_CSCALE
 #define EB_HSCALE (MGB_ERFCX_CSCALE / EB_KAPPA)
 #define EB_ZS_SKIP 12.4f   // |zs| beyond which g and q flush to zero
 // Gaussian recurrence: used for a tile while every object is within za_lim of
 // the group's central edge (in zs units), za_lim = min(EB_ZA_MAX,
-// (EB_CHAIN_EXP_MAX - (ET+1) d^2) / (2 d)): the exponent of every ratio then
+// (EB_CHAIN_EXP_MAX - J^2 d^2) / (2 J d)): the exponent of every ratio then
 // stays below EB_CHAIN_EXP_MAX in magnitude, which bounds the relative error
 // a ratio inherits from the fp32 rounding of its exponent to
-// EB_CHAIN_EXP_MAX * 2^-24 * ln 2 = 6.6e-7 (and keeps everything finite).
+// EB_CHAIN_EXP_MAX * 2^-24 * ln 2 = 1e-6 (and keeps everything finite).
 #define EB_ZA_MAX 10.0f
-#define EB_CHAIN_EXP_MAX 16.0
+#define EB_CHAIN_EXP_MAX 24.0
 
 // ------------------------------------------------------------ cluster / DSMEM
 __device__ __forceinline__ unsigned eb_cluster_ctarank() {
@@ -147,46 +147,41 @@ struct EdgeAcc {
   float T, O, G, Z;
 };
 
-#ifndef EB_CHAIN_LEN
-#define EB_CHAIN_LEN 2
+// Gaussian recurrence (uniform edges).  With A0 = ET/2 the central edge of a
+// group, zs_{A0+k} = za + k d and
+//     g_{A0+k} = 2^(-zs_{A0+k}^2) = g_{A0+k-1} rho_k,
+//     rho_k = 2^(-2 za d - (2k-1) d^2) = rho_1 kap^(k-1),  kap = 2^(-2 d^2)
+// (downward: d -> -d).  MUFU.EX2 supplies g_A0, rho_1 of both directions and,
+// EB_SKIP edges away from the centre, the direct ratio g_{A0+-J} / g_A0 =
+// 2^(-+2 J za d - J^2 d^2), from which the recurrence restarts: no Gaussian
+// is more than EB_SKIP - 1 multiplications by a MUFU-derived ratio away from
+// one that MUFU.EX2 delivered, and all of them inherit the rounding of g_A0,
+// so that differences between neighbouring edges (the mu-Jacobian) stay
+// accurate for wide Gaussians.  7 to 10 MUFU.EX2 per pair of objects and
+// group instead of 2 per edge.
+#ifndef EB_SKIP
+#define EB_SKIP 3
 #endif
-// Segments of S = 2*EB_CHAIN_LEN + 1 consecutive edges of a group of ET edges;
-// the middle edge of a segment is its anchor.
-template <int ET>
-struct EbSeg {
-  static constexpr int S = 2 * EB_CHAIN_LEN + 1 < ET ? 2 * EB_CHAIN_LEN + 1
-                                                     : ET;
-  static constexpr int NSEG = (ET + S - 1) / S;
-  static constexpr int A0 = ET / 2;  // central edge: Z' anchor, base ratios
-  __host__ __device__ static constexpr int first(int sg) { return sg * S; }
-  __host__ __device__ static constexpr int count(int sg) {
-    return (sg + 1) * S <= ET ? S : ET - sg * S;
-  }
-  __host__ __device__ static constexpr int anchor(int sg) {
-    return first(sg) + count(sg) / 2;
-  }
-};
+#ifndef EB_CHUNK
+#define EB_CHUNK 4
+#endif
 
 // warp-uniform constants of one edge group for the current parameters
 template <int ET>
 struct GroupConst {
-  float cw[ET];     // w_e = cw[e] - kw*xc,  w = EB_HSCALE * zs
-  float kw;         // EB_HSCALE * ks
+  float cs[ET];     // zs_e = cs[e] - ks*xc
   float ks;         // kappa / (sqrt2 sigma)
-  float csa;        // zs at the central edge = csa - ks*xc
-  float cs_lo, cs_hi;  // zs-scaled first / last edge of the group (skip test)
   float two_d;      // 2 d,  d = ks * bin width
   float nd2;        // -d^2
   float kap;        // 2^(-2 d^2)
-  float csn[EbSeg<ET>::NSEG];  // zs-scaled anchor edge of every segment
-  float kup[EbSeg<ET>::NSEG];  // kap^(anchor - A0)
-  float kdn[EbSeg<ET>::NSEG];  // kap^(A0 - anchor)
+  float two_jd;     // 2 J d          (J = EB_SKIP)
+  float nj2d2;      // -J^2 d^2
+  float kapj;       // kap^J: rho_{J+1} = rho_1 kap^J
   float za_lim;     // recurrence allowed while |zs_A0| <= za_lim (<= 0: never)
-  const float* cs;  // shared memory: zs-scaled edges of the group (per-edge path)
 };
 
-// t, Horner polynomial and the four accumulations for up to CH consecutive
-// edges of a group starting at edge `base` (i < nvalid).
+// t, Horner polynomial and the four accumulations for up to CH edges of a
+// group: edge i of the chunk is edge `base + dir*i` of the group (i < nvalid).
 //
 // The chains of the chunk are written *stage by stage* (all edges do step i
 // before any edge does step i+1): ptxas keeps that order, so every warp has CH
@@ -194,14 +189,18 @@ struct GroupConst {
 // its latency.
 template <int CH, bool WEIGHTED>
 __device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
-                                         int nvalid, const float2* w,
-                                         const float2* g, float2 za,
-                                         float2 wt) {
+                                         int dir, int nvalid, const float2* zs,
+                                         const float2* g, float2 wt) {
   float2 t[CH], p[CH];
 #pragma unroll
-  for (int i = 0; i < CH; ++i)
-    if (i < nvalid)
-      t[i] = f2(mgb_rcp(1.0f + fabsf(w[i].x)), mgb_rcp(1.0f + fabsf(w[i].y)));
+  for (int i = 0; i < CH; ++i) {
+    if (i < nvalid) {
+      // t = 1/(1 + h |zs|): the |.| is an operand modifier of the FFMA2
+      const float2 d = vfma(f2(fabsf(zs[i].x), fabsf(zs[i].y)),
+                            f2s(EB_HSCALE), f2s(1.0f));
+      t[i] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
+    }
+  }
   // coefficients pre-halved so that p = erfcx/2 / t
   constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
@@ -221,13 +220,14 @@ __device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
 #pragma unroll
   for (int i = 0; i < CH; ++i) {
     if (i < nvalid) {
-      EdgeAcc& ac = a[base + i];
+      EdgeAcc& ac = a[base + dir * i];
       // T += +q for z < 0, -q for z >= 0, q = p*g = (weight) 1/2 erfc(|z|):
-      // the sign goes onto g (sign bit from ~sign(w)), the product into the FMA
+      // the sign goes onto g (sign bit from ~sign(zs)), the product into the
+      // FMA
       const float gx = __uint_as_float(
-          __float_as_uint(g[i].x) | (~__float_as_uint(w[i].x) & 0x80000000u));
+          __float_as_uint(g[i].x) | (~__float_as_uint(zs[i].x) & 0x80000000u));
       const float gy = __uint_as_float(
-          __float_as_uint(g[i].y) | (~__float_as_uint(w[i].y) & 0x80000000u));
+          __float_as_uint(g[i].y) | (~__float_as_uint(zs[i].y) & 0x80000000u));
       ac.T = fmaf(p[i].x, gx, ac.T);
       ac.T = fmaf(p[i].y, gy, ac.T);
     }
@@ -235,16 +235,16 @@ __device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
 #pragma unroll
   for (int i = 0; i < CH; ++i) {
     if (i < nvalid) {
-      EdgeAcc& ac = a[base + i];
+      EdgeAcc& ac = a[base + dir * i];
       if (WEIGHTED) {
-        ac.O += w[i].x >= 0.0f ? wt.x : 0.0f;
-        ac.O += w[i].y >= 0.0f ? wt.y : 0.0f;
+        ac.O += zs[i].x >= 0.0f ? wt.x : 0.0f;
+        ac.O += zs[i].y >= 0.0f ? wt.y : 0.0f;
       } else {
         // unweighted: count the objects *below* the edge on the integer pipe
-        // (sign bit of w; the bit pattern of O is an int32 counter)
+        // (sign bit of zs; the bit pattern of O is an int32 counter)
         int cnt = __float_as_int(ac.O);
-        cnt += (int)(__float_as_uint(w[i].x) >> 31);
-        cnt += (int)(__float_as_uint(w[i].y) >> 31);
+        cnt += (int)(__float_as_uint(zs[i].x) >> 31);
+        cnt += (int)(__float_as_uint(zs[i].y) >> 31);
         ac.O = __int_as_float(cnt);
       }
     }
@@ -252,91 +252,123 @@ __device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
 #pragma unroll
   for (int i = 0; i < CH; ++i) {
     if (i < nvalid) {
-      EdgeAcc& ac = a[base + i];
+      EdgeAcc& ac = a[base + dir * i];
       ac.G += g[i].x;
       ac.G += g[i].y;
-      ac.Z = fmaf(za.x, g[i].x, ac.Z);
-      ac.Z = fmaf(za.y, g[i].y, ac.Z);
+      ac.Z = fmaf(zs[i].x, g[i].x, ac.Z);
+      ac.Z = fmaf(zs[i].y, g[i].y, ac.Z);
     }
   }
 }
 
-// Gaussian of a pair at scaled coordinate zs = cs - ks*xc: g = 2^(-zs^2)
+// Gaussian of a pair: g = 2^(-zs^2)
 template <bool WEIGHTED>
-__device__ __forceinline__ float2 eb_gauss(float2 xc, float ks, float cs,
-                                           float2 wt) {
-  const float2 zs = vfma(xc, f2s(-ks), f2s(cs));
+__device__ __forceinline__ float2 eb_gauss(float2 zs, float2 wt) {
   const float2 zz = vmul(zs, zs);
   float2 g = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
   if (WEIGHTED) g = vmul(g, wt);
   return g;
 }
 
+// Gaussians of the chunk of edges A0 + sgn*k, k = k0 .. k0+n-1, continuing the
+// recurrence state (gc = Gaussian of the previous edge, r = next ratio).
+template <int CH>
+__device__ __forceinline__ void eb_chain(float2* g, int k0, int n, int kmax,
+                                         float2 ga, float2 r1, float2 rj,
+                                         float kap, float kapj, float2& gc,
+                                         float2& r) {
+#pragma unroll
+  for (int i = 0; i < CH; ++i) {
+    if (i < n) {
+      const int k = k0 + i;
+      if (k == 0) {
+        gc = ga;
+      } else if (k == EB_SKIP) {
+        gc = vmul(ga, rj);                      // direct ratio from the centre
+        if (k < kmax) r = vmul(r1, f2s(kapj));  // rho_{J+1}
+      } else {
+        gc = vmul(gc, r);
+        if (k < kmax && k + 1 != EB_SKIP) r = vmul(r, f2s(kap));
+      }
+      g[i] = gc;
+    }
+  }
+}
+
 // Contribution of a pair of objects (centred coordinate xc, weight wt) to the
-// accumulators of the ET edges of a group, segment by segment.
-// CHAIN: only the anchor of a segment gets its Gaussian from MUFU.EX2; the
-// others follow by the recurrence
-//   upward    g_{e+1} = g_e rho_e,   rho_e = 2^(-2 zs_e d - d^2),
-//             rho_{e+1} = rho_e 2^(-2 d^2)
-//   downward  the same with d -> -d,
-// where rho at the first step of a segment is a per-object base ratio (one
-// MUFU.EX2 per direction, formed at the group's central edge A0) times a
-// per-segment constant.  At most EB_CHAIN_LEN ratios are multiplied up, which
-// bounds the accumulated relative error to about EB_CHAIN_LEN MUFU errors.
+// accumulators of the ET edges of a group, in chunks of EB_CHUNK edges outward
+// from the central edge (first upward, then downward).  CHAIN selects the
+// recurrence; otherwise every edge gets its own MUFU.EX2.
 template <int ET, bool WEIGHTED, bool CHAIN>
 __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
                                            const GroupConst<ET>& c, float2 xc,
                                            float2 wt) {
-  typedef EbSeg<ET> SG;
-  constexpr int S = SG::S;
-  const float2 za = vfma(xc, f2s(-c.ks), f2s(c.csa));
-  float2 ru = f2s(0.f), rd = f2s(0.f);
-  if (CHAIN && S > 1) {
-    const float2 eu = vfma(za, f2s(-c.two_d), f2s(c.nd2));
-    ru = f2(mgb_ex2(eu.x), mgb_ex2(eu.y));
-    const float2 ed = vfma(za, f2s(c.two_d), f2s(c.nd2));
-    rd = f2(mgb_ex2(ed.x), mgb_ex2(ed.y));
-  }
-#pragma unroll
-  for (int sg = 0; sg < SG::NSEG; ++sg) {
-    const int e0 = SG::first(sg), n = SG::count(sg), an = SG::anchor(sg);
-    float2 w[S], g[S];
-#pragma unroll
-    for (int i = 0; i < S; ++i)
-      if (i < n) w[i] = vfma(xc, f2s(-c.kw), f2s(c.cw[e0 + i]));
-    if (CHAIN) {
-      const int ia = an - e0;
-      g[ia] = eb_gauss<WEIGHTED>(xc, c.ks, c.csn[sg], wt);
-      // ratio of the step an -> an+1 is ru * kap^(an - A0); of the step
-      // an -> an-1 it is rd * kap^(A0 - an)
-      if (ia + 1 < n) {
-        float2 r = vmul(ru, f2s(c.kup[sg]));
-        float2 gc = g[ia];
-#pragma unroll
-        for (int i = ia + 1; i < S; ++i) {
-          if (i < n) {
-            gc = vmul(gc, r);
-            g[i] = gc;
-            if (i + 1 < n) r = vmul(r, f2s(c.kap));
-          }
-        }
-      }
-      if (ia > 0) {
-        float2 r = vmul(rd, f2s(c.kdn[sg]));
-        float2 gc = g[ia];
-#pragma unroll
-        for (int i = ia - 1; i >= 0; --i) {
-          gc = vmul(gc, r);
-          g[i] = gc;
-          if (i > 0) r = vmul(r, f2s(c.kap));
-        }
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < S; ++i)
-        if (i < n) g[i] = eb_gauss<WEIGHTED>(xc, c.ks, c.cs[e0 + i], wt);
+  constexpr int A0 = ET / 2;
+  constexpr int CH = EB_CHUNK < ET ? EB_CHUNK : ET;
+  constexpr int KU = ET - 1 - A0, KD = A0;  // edges above / below the centre
+  float2 ga = f2s(0.f), ru = f2s(0.f), rd = f2s(0.f), rju = f2s(0.f),
+         rjd = f2s(0.f);
+  if (CHAIN) {
+    // (the same rounded zs as the one the central edge's chunk uses: all
+    // quantities of an object derive from ONE coordinate per edge)
+    const float2 za = vfma(xc, f2s(-c.ks), f2s(c.cs[A0]));
+    const float2 zz = vmul(za, za);
+    ga = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
+    if (WEIGHTED) ga = vmul(ga, wt);
+    if (KU >= 1) {
+      const float2 e = vfma(za, f2s(-c.two_d), f2s(c.nd2));
+      ru = f2(mgb_ex2(e.x), mgb_ex2(e.y));
     }
-    eb_chunk<S, WEIGHTED>(a, e0, n, w, g, za, wt);
+    if (KD >= 1) {
+      const float2 e = vfma(za, f2s(c.two_d), f2s(c.nd2));
+      rd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+    }
+    if (KU >= EB_SKIP) {
+      const float2 e = vfma(za, f2s(-c.two_jd), f2s(c.nj2d2));
+      rju = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+    }
+    if (KD >= EB_SKIP) {
+      const float2 e = vfma(za, f2s(c.two_jd), f2s(c.nj2d2));
+      rjd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+    }
+  }
+  {
+    float2 gc = ga, r = ru;
+#pragma unroll
+    for (int b0 = A0; b0 < ET; b0 += CH) {       // edges b0, b0+1, ...
+      float2 zs[CH], g[CH];
+#pragma unroll
+      for (int i = 0; i < CH; ++i)
+        if (b0 + i < ET) zs[i] = vfma(xc, f2s(-c.ks), f2s(c.cs[b0 + i]));
+      if (CHAIN) {
+        eb_chain<CH>(g, b0 - A0, ET - b0, KU, ga, ru, rju, c.kap, c.kapj, gc,
+                     r);
+      } else {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (b0 + i < ET) g[i] = eb_gauss<WEIGHTED>(zs[i], wt);
+      }
+      eb_chunk<CH, WEIGHTED>(a, b0, 1, ET - b0, zs, g, wt);
+    }
+  }
+  {
+    float2 gc = ga, r = rd;
+#pragma unroll
+    for (int b1 = A0 - 1; b1 >= 0; b1 -= CH) {   // edges b1, b1-1, ...
+      float2 zs[CH], g[CH];
+#pragma unroll
+      for (int i = 0; i < CH; ++i)
+        if (b1 - i >= 0) zs[i] = vfma(xc, f2s(-c.ks), f2s(c.cs[b1 - i]));
+      if (CHAIN) {
+        eb_chain<CH>(g, A0 - b1, b1 + 1, KD, ga, rd, rjd, c.kap, c.kapj, gc,
+                     r);
+      } else {
+#pragma unroll
+        for (int i = 0; i < CH; ++i)
+          if (b1 - i >= 0) g[i] = eb_gauss<WEIGHTED>(zs[i], wt);
+      }
+      eb_chunk<CH, WEIGHTED>(a, b1, -1, b1 + 1, zs, g, wt);
+    }
   }
 }
 
@@ -362,11 +394,15 @@ __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
 #define EB_MAX_WARPS 12
 #endif
 #ifndef EB_WIDE_WARPS
-#define EB_WIDE_WARPS 8
+#define EB_WIDE_WARPS 12
 #endif
-// groups of more than EB_ET_NARROW edges run in CTAs of EB_WIDE_WARPS warps
-// compiled for 128 registers, the narrow ones in CTAs of up to EB_MAX_WARPS
-// warps at 80
+#ifndef EB_WIDE_CTAS
+#define EB_WIDE_CTAS 1
+#endif
+// groups of more than EB_ET_NARROW edges run in EB_WIDE_CTAS CTA(s) per SM of
+// EB_WIDE_WARPS warps (12 warps at up to 168 registers: measured 8% faster
+// than 2 x 8 warps at 128), the narrow ones in CTAs of up to EB_MAX_WARPS warps
+// at 80 registers
 #ifndef EB_ET_NARROW
 #define EB_ET_NARROW 4
 #endif
@@ -376,6 +412,9 @@ __device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
 
 constexpr int eb_block_threads(int et_hi) {
   return et_hi > EB_ET_NARROW ? EB_WIDE_WARPS * 32 : EB_MAX_WARPS * 32;
+}
+constexpr int eb_min_ctas(int et_hi) {
+  return et_hi > EB_ET_NARROW ? EB_WIDE_CTAS : EB_MIN_CTAS;
 }
 constexpr int eb_smem_warps() {
   return EB_WIDE_WARPS > EB_MAX_WARPS ? EB_WIDE_WARPS : EB_MAX_WARPS;
@@ -428,7 +467,7 @@ __device__ __forceinline__ void eb_fetch(const MgbErfBinModel& md,
 
 // Accumulate the ET edges of a group over the tiles of this CTA that belong
 // to warp `wj` of `wpg` warps in the group; leave the warp-reduced sums
-// (T, O, G, Z' per edge) in s_out[4*ET] (lane 0 writes).  `first` holds the
+// (T, O, G, Z per edge) in s_out[4*ET] (lane 0 writes).  `first` holds the
 // warp's first tile, fetched by the caller (in the persistent fit before it
 // waits for the parameters of the step).
 template <int ET, bool WEIGHTED>
@@ -459,15 +498,15 @@ __device__ __forceinline__ void accumulate_group(
     // nothing to any difference between edges: skip them warp-uniformly
     const float cmin = fminf(fminf(xcA.x, xcA.y), fminf(xcB.x, xcB.y));
     const float cmax = fmaxf(fmaxf(xcA.x, xcA.y), fmaxf(xcB.x, xcB.y));
-    const bool far = (fmaf(-c.ks, cmax, c.cs_lo) > EB_ZS_SKIP) ||
-                     (fmaf(-c.ks, cmin, c.cs_hi) < -EB_ZS_SKIP);
+    const bool far = (fmaf(-c.ks, cmax, c.cs[0]) > EB_ZS_SKIP) ||
+                     (fmaf(-c.ks, cmin, c.cs[ET - 1]) < -EB_ZS_SKIP);
     if (__all_sync(0xffffffffu, far)) {
       // A skipped lane still has to keep the hard counts consistent with the
       // other edge groups, for which the same objects may not be saturated.
       if (WEIGHTED) {
         // O = weight of objects at or above the edge: all four objects of a
         // lane that is saturated on the high side (padding has weight 0)
-        if (fmaf(-c.ks, cmax, c.cs_lo) > EB_ZS_SKIP) {
+        if (fmaf(-c.ks, cmax, c.cs[0]) > EB_ZS_SKIP) {
           const float cnt = (wv.x + wv.y) + (wv.z + wv.w);
 #pragma unroll
           for (int e = 0; e < ET; ++e) acc[e].O += cnt;
@@ -476,7 +515,7 @@ __device__ __forceinline__ void accumulate_group(
         // O = number of objects below the edge: all four objects of a lane
         // saturated on the low side (padding objects sit there too, in every
         // group alike, so they cancel in the differences between edges)
-        if (fmaf(-c.ks, cmin, c.cs_hi) < -EB_ZS_SKIP) {
+        if (fmaf(-c.ks, cmin, c.cs[ET - 1]) < -EB_ZS_SKIP) {
 #pragma unroll
           for (int e = 0; e < ET; ++e)
             acc[e].O = __int_as_float(__float_as_int(acc[e].O) + 4);
@@ -486,8 +525,8 @@ __device__ __forceinline__ void accumulate_group(
     }
     // the recurrence needs every object of the tile within za_lim of the
     // central edge (in zs units); zs is monotone in xc
-    const bool near = fmaxf(fabsf(fmaf(-c.ks, cmax, c.csa)),
-                            fabsf(fmaf(-c.ks, cmin, c.csa))) <= c.za_lim;
+    const bool near = fmaxf(fabsf(fmaf(-c.ks, cmax, c.cs[ET / 2])),
+                            fabsf(fmaf(-c.ks, cmin, c.cs[ET / 2]))) <= c.za_lim;
     // the two pairs of a lane go through the same code one after the other
     // (not inlined twice: the wide kernels would not fit the instruction
     // caches)
@@ -526,8 +565,6 @@ __device__ __forceinline__ void accumulate_group(
 // per-step shared state of a CTA
 struct EbShared {
   float cs[EB_MAX_EDGES];              // zs-scaled centred edges
-  float cw[EB_MAX_EDGES];              // the same times EB_HSCALE (w units)
-  double dz[EB_MAX_EDGES];             // cs_e - cs_centre(e) in fp64
   double warp[eb_smem_warps()][4 * EB_ET_MAX];
   double edge[EB_MAX_EDGES][4];
   double clu[EB_MAX_CLUSTER * 3 * MGB_MAX_BINS];  // leader: pushed partials
@@ -546,30 +583,22 @@ __device__ __forceinline__ void run_group(const MgbErfBinModel& md,
                                           int e_first, int wj, int wpg,
                                           int warp, int lane,
                                           const EbTile& first) {
-  typedef EbSeg<ET> SG;
   GroupConst<ET> c;
   c.ks = (float)ks_d;
-  c.kw = (float)(ks_d * (double)EB_HSCALE);
 #pragma unroll
-  for (int e = 0; e < ET; ++e) c.cw[e] = sh.cw[e_first + e];
-  c.cs = sh.cs + e_first;
-  c.csa = sh.cs[e_first + SG::A0];
-  c.cs_lo = sh.cs[e_first];
-  c.cs_hi = sh.cs[e_first + ET - 1];
+  for (int e = 0; e < ET; ++e) c.cs[e] = sh.cs[e_first + e];
   const double d = ks_d * width;
   c.two_d = (float)(2.0 * d);
   c.nd2 = (float)(-d * d);
-  c.kap = exp2f(-2.0f * (float)(d * d));
-#pragma unroll
-  for (int sg = 0; sg < SG::NSEG; ++sg) {
-    const float da = (float)(SG::anchor(sg) - SG::A0);
-    c.csn[sg] = sh.cs[e_first + SG::anchor(sg)];
-    c.kup[sg] = exp2f(-2.0f * (float)(d * d) * da);
-    c.kdn[sg] = exp2f(2.0f * (float)(d * d) * da);
-  }
+  c.kap = (float)exp2(-2.0 * d * d);
+  c.two_jd = (float)(2.0 * EB_SKIP * d);
+  c.nj2d2 = (float)(-(double)(EB_SKIP * EB_SKIP) * d * d);
+  c.kapj = (float)exp2(-2.0 * EB_SKIP * d * d);
   c.za_lim = 0.f;
   if (uniform && ET > 1) {
-    const double lim = (EB_CHAIN_EXP_MAX - (ET + 1) * d * d) / (2.0 * d);
+    // largest exponent: the skip ratio, 2 J |za| d + J^2 d^2
+    const double lim = (EB_CHAIN_EXP_MAX - EB_SKIP * EB_SKIP * d * d) /
+                       (2.0 * EB_SKIP * d);
     c.za_lim = (float)(lim < (double)EB_ZA_MAX ? lim : (double)EB_ZA_MAX);
   }
   accumulate_group<ET, WEIGHTED>(md, c, md.x0, wj, wpg, lane, first,
@@ -577,7 +606,7 @@ __device__ __forceinline__ void run_group(const MgbErfBinModel& md,
 }
 
 template <int ET_HI, bool WEIGHTED>
-__global__ void __launch_bounds__(eb_block_threads(ET_HI), EB_MIN_CTAS)
+__global__ void __launch_bounds__(eb_block_threads(ET_HI), eb_min_ctas(ET_HI))
 erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
                    const __grid_constant__ MgbStepArgs a,
                    const __grid_constant__ MgbPeerTable pt,
@@ -745,15 +774,8 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     // cs_e is formed in fp64 so that zs never subtracts two O(10) numbers.
     const double ks_d = 1.2011224087864498 * 0.7071067811865476 / sigma_d;
     if (tid < E) {
-      const double csd =
-          (md.edges[tid] - ((double)p_mu + (double)md.x0)) * ks_d;
-      sh.cs[tid] = (float)csd;
-      sh.cw[tid] = (float)(csd * (double)EB_HSCALE);
-      // offset of this edge from the central edge of its group (Z' -> Z)
-      int g2 = 0;
-      while (g2 + 1 < lay.ng && tid >= lay.e0[g2 + 1]) ++g2;
-      const int centre = lay.e0[g2] + (lay.e0[g2 + 1] - lay.e0[g2]) / 2;
-      sh.dz[tid] = (md.edges[tid] - md.edges[centre]) * ks_d;
+      sh.cs[tid] =
+          (float)((md.edges[tid] - ((double)p_mu + (double)md.x0)) * ks_d);
     }
     __syncthreads();
 
@@ -806,9 +828,7 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
         } else if (q == 1) {
           val = sh.edge[k + 1][2] - sh.edge[k][2];
         } else {
-          // Z_e = Z'_e + (cs_e - cs_centre) G_e
-          val = (sh.edge[k + 1][3] + sh.dz[k + 1] * sh.edge[k + 1][2]) -
-                (sh.edge[k][3] + sh.dz[k] * sh.edge[k][2]);
+          val = sh.edge[k + 1][3] - sh.edge[k][3];
         }
         eb_st_cluster_f64(dst + (unsigned)((crank * MP + j) * 8), val);
       }
@@ -1044,7 +1064,7 @@ int sm_count() {
 }
 
 // CTAs per SM so that about EB_TARGET_WARPS warps are resident (the wide
-// kernels are compiled for EB_MIN_CTAS CTAs of 128 registers)
+// kernels run EB_WIDE_CTAS CTA(s) per SM)
 int grid_for(int nbins) {
   MgbErfBinModel tmp;
   memset(&tmp, 0, sizeof(tmp));
@@ -1052,7 +1072,7 @@ int grid_for(int nbins) {
   int et_hi = 0;
   const int nwarps = make_layout(tmp, &et_hi).nwarps;
   int per_sm = EB_TARGET_WARPS / nwarps;
-  const int cap = et_hi > EB_ET_NARROW ? EB_MIN_CTAS : 8;
+  const int cap = et_hi > EB_ET_NARROW ? EB_WIDE_CTAS : 8;
   if (per_sm < 1) per_sm = 1;
   if (per_sm > cap) per_sm = cap;
   return sm_count() * per_sm;
