@@ -163,7 +163,10 @@ struct EdgeAcc {
 #define EB_SKIP 3
 #endif
 #ifndef EB_CHUNK
-#define EB_CHUNK 4
+#define EB_CHUNK 3
+#endif
+#ifndef EB_FLAT
+#define EB_FLAT 0
 #endif
 
 // warp-uniform constants of one edge group for the current parameters
@@ -180,195 +183,215 @@ struct GroupConst {
   float za_lim;     // recurrence allowed while |zs_A0| <= za_lim (<= 0: never)
 };
 
-// t, Horner polynomial and the four accumulations for up to CH edges of a
-// group: edge i of the chunk is edge `base + dir*i` of the group (i < nvalid).
-//
-// The chains of the chunk are written *stage by stage* (all edges do step i
-// before any edge does step i+1): ptxas keeps that order, so every warp has CH
-// independent FFMA2 streams in flight and the Horner recurrence never exposes
-// its latency.
-template <int CH, bool WEIGHTED>
-__device__ __forceinline__ void eb_chunk(EdgeAcc* __restrict__ a, int base,
-                                         int dir, int nvalid, const float2* zs,
-                                         const float2* g, float2 wt) {
-  float2 t[CH], p[CH];
+// Processing order of the ET edges of a group: the central edge A0 first,
+// then upward to the last edge, then downward from A0-1 to edge 0 (the order
+// in which the recurrence produces the Gaussians).
+template <int ET>
+struct EbOrd {
+  static constexpr int A0 = ET / 2;
+  static constexpr int KU = ET - 1 - A0;  // edges above the centre
+  static constexpr int KD = A0;           // edges below it
+  __host__ __device__ static constexpr int edge(int i) {
+    return i <= KU ? A0 + i : A0 - (i - KU);
+  }
+  // signed distance from the centre in units of the bin width
+  __host__ __device__ static constexpr int k(int i) {
+    return i <= KU ? i : -(i - KU);
+  }
+};
+
+// per-object state of the Gaussian recurrence
+struct EbChain {
+  float2 ga;        // Gaussian of the central edge (times the weight)
+  float2 ru, rd;    // rho_1 upward / downward
+  float2 rju, rjd;  // direct ratio g_{A0+-J} / g_A0
+  float2 gc, r;     // Gaussian of the previous edge, next ratio
+};
+
+// Stage A of a chunk (edges ord(i0) .. ord(i0+CH-1)): scaled coordinate,
+// Gaussian and t = 1/(1 + h |zs|) of every edge -- all the MUFU work.
+template <int ET, int CH, bool WEIGHTED, bool CHAIN>
+__device__ __forceinline__ void eb_stage_a(const GroupConst<ET>& c, float2 xc,
+                                           float2 wt, int i0, EbChain& ch,
+                                           float2* zs, float2* g, float2* t) {
+  typedef EbOrd<ET> OD;
 #pragma unroll
-  for (int i = 0; i < CH; ++i) {
-    if (i < nvalid) {
-      // t = 1/(1 + h |zs|): the |.| is an operand modifier of the FFMA2
-      const float2 d = vfma(f2(fabsf(zs[i].x), fabsf(zs[i].y)),
+  for (int j = 0; j < CH; ++j)
+    if (i0 + j < ET)
+      zs[j] = vfma(xc, f2s(-c.ks), f2s(c.cs[OD::edge(i0 + j)]));
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (i0 + j < ET) {
+      // the |.| is an operand modifier of the FFMA2
+      const float2 d = vfma(f2(fabsf(zs[j].x), fabsf(zs[j].y)),
                             f2s(EB_HSCALE), f2s(1.0f));
-      t[i] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
+      t[j] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
     }
   }
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (i0 + j < ET) {
+      if (CHAIN) {
+        const int k = OD::k(i0 + j);
+        const int ak = k < 0 ? -k : k;
+        const int kmax = k < 0 ? OD::KD : OD::KU;
+        if (k == 0) {
+          ch.gc = ch.ga;
+          ch.r = ch.ru;
+        } else if (k == -1) {          // the downward run starts at the centre
+          ch.gc = vmul(ch.ga, ch.rd);
+          ch.r = vmul(ch.rd, f2s(c.kap));
+        } else if (ak == EB_SKIP) {    // direct ratio from the centre
+          ch.gc = vmul(ch.ga, k > 0 ? ch.rju : ch.rjd);
+          if (ak < kmax) ch.r = vmul(k > 0 ? ch.ru : ch.rd, f2s(c.kapj));
+        } else {
+          ch.gc = vmul(ch.gc, ch.r);
+          if (ak < kmax && ak + 1 != EB_SKIP) ch.r = vmul(ch.r, f2s(c.kap));
+        }
+        g[j] = ch.gc;
+      } else {
+        const float2 zz = vmul(zs[j], zs[j]);
+        g[j] = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
+        if (WEIGHTED) g[j] = vmul(g[j], wt);
+      }
+    }
+  }
+}
+
+// Stage B of a chunk: Horner polynomial and the four accumulations -- all
+// FMA-pipe work.  The chains of the chunk are written *stage by stage* (all
+// edges do step i before any edge does step i+1): ptxas keeps that order, so
+// every warp has CH independent FFMA2 streams in flight and the Horner
+// recurrence never exposes its latency.
+template <int ET, int CH, bool WEIGHTED>
+__device__ __forceinline__ void eb_stage_b(EdgeAcc* __restrict__ a, int i0,
+                                           const float2* zs, const float2* g,
+                                           const float2* t, float2 wt) {
+  typedef EbOrd<ET> OD;
+  float2 p[CH];
   // coefficients pre-halved so that p = erfcx/2 / t
   constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
-  for (int i = 0; i < CH; ++i)
-    if (i < nvalid)
-      p[i] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[i],
+  for (int j = 0; j < CH; ++j)
+    if (i0 + j < ET)
+      p[j] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[j],
                   f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
 #pragma unroll
   for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
 #pragma unroll
-    for (int i = 0; i < CH; ++i)
-      if (i < nvalid) p[i] = vfma(p[i], t[i], f2s(0.5f * kC[d]));
+    for (int j = 0; j < CH; ++j)
+      if (i0 + j < ET) p[j] = vfma(p[j], t[j], f2s(0.5f * kC[d]));
   }
 #pragma unroll
-  for (int i = 0; i < CH; ++i)
-    if (i < nvalid) p[i] = vmul(p[i], t[i]);
+  for (int j = 0; j < CH; ++j)
+    if (i0 + j < ET) p[j] = vmul(p[j], t[j]);
 #pragma unroll
-  for (int i = 0; i < CH; ++i) {
-    if (i < nvalid) {
-      EdgeAcc& ac = a[base + dir * i];
+  for (int j = 0; j < CH; ++j) {
+    if (i0 + j < ET) {
+      EdgeAcc& ac = a[OD::edge(i0 + j)];
       // T += +q for z < 0, -q for z >= 0, q = p*g = (weight) 1/2 erfc(|z|):
       // the sign goes onto g (sign bit from ~sign(zs)), the product into the
       // FMA
       const float gx = __uint_as_float(
-          __float_as_uint(g[i].x) | (~__float_as_uint(zs[i].x) & 0x80000000u));
+          __float_as_uint(g[j].x) | (~__float_as_uint(zs[j].x) & 0x80000000u));
       const float gy = __uint_as_float(
-          __float_as_uint(g[i].y) | (~__float_as_uint(zs[i].y) & 0x80000000u));
-      ac.T = fmaf(p[i].x, gx, ac.T);
-      ac.T = fmaf(p[i].y, gy, ac.T);
+          __float_as_uint(g[j].y) | (~__float_as_uint(zs[j].y) & 0x80000000u));
+      ac.T = fmaf(p[j].x, gx, ac.T);
+      ac.T = fmaf(p[j].y, gy, ac.T);
     }
   }
 #pragma unroll
-  for (int i = 0; i < CH; ++i) {
-    if (i < nvalid) {
-      EdgeAcc& ac = a[base + dir * i];
+  for (int j = 0; j < CH; ++j) {
+    if (i0 + j < ET) {
+      EdgeAcc& ac = a[OD::edge(i0 + j)];
       if (WEIGHTED) {
-        ac.O += zs[i].x >= 0.0f ? wt.x : 0.0f;
-        ac.O += zs[i].y >= 0.0f ? wt.y : 0.0f;
+        ac.O += zs[j].x >= 0.0f ? wt.x : 0.0f;
+        ac.O += zs[j].y >= 0.0f ? wt.y : 0.0f;
       } else {
         // unweighted: count the objects *below* the edge on the integer pipe
         // (sign bit of zs; the bit pattern of O is an int32 counter)
         int cnt = __float_as_int(ac.O);
-        cnt += (int)(__float_as_uint(zs[i].x) >> 31);
-        cnt += (int)(__float_as_uint(zs[i].y) >> 31);
+        cnt += (int)(__float_as_uint(zs[j].x) >> 31);
+        cnt += (int)(__float_as_uint(zs[j].y) >> 31);
         ac.O = __int_as_float(cnt);
       }
     }
   }
 #pragma unroll
-  for (int i = 0; i < CH; ++i) {
-    if (i < nvalid) {
-      EdgeAcc& ac = a[base + dir * i];
-      ac.G += g[i].x;
-      ac.G += g[i].y;
-      ac.Z = fmaf(zs[i].x, g[i].x, ac.Z);
-      ac.Z = fmaf(zs[i].y, g[i].y, ac.Z);
+  for (int j = 0; j < CH; ++j) {
+    if (i0 + j < ET) {
+      EdgeAcc& ac = a[OD::edge(i0 + j)];
+      ac.G += g[j].x;
+      ac.G += g[j].y;
+      ac.Z = fmaf(zs[j].x, g[j].x, ac.Z);
+      ac.Z = fmaf(zs[j].y, g[j].y, ac.Z);
     }
   }
 }
 
-// Gaussian of a pair: g = 2^(-zs^2)
-template <bool WEIGHTED>
-__device__ __forceinline__ float2 eb_gauss(float2 zs, float2 wt) {
-  const float2 zz = vmul(zs, zs);
-  float2 g = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
-  if (WEIGHTED) g = vmul(g, wt);
-  return g;
-}
-
-// Gaussians of the chunk of edges A0 + sgn*k, k = k0 .. k0+n-1, continuing the
-// recurrence state (gc = Gaussian of the previous edge, r = next ratio).
-template <int CH>
-__device__ __forceinline__ void eb_chain(float2* g, int k0, int n, int kmax,
-                                         float2 ga, float2 r1, float2 rj,
-                                         float kap, float kapj, float2& gc,
-                                         float2& r) {
-#pragma unroll
-  for (int i = 0; i < CH; ++i) {
-    if (i < n) {
-      const int k = k0 + i;
-      if (k == 0) {
-        gc = ga;
-      } else if (k == EB_SKIP) {
-        gc = vmul(ga, rj);                      // direct ratio from the centre
-        if (k < kmax) r = vmul(r1, f2s(kapj));  // rho_{J+1}
-      } else {
-        gc = vmul(gc, r);
-        if (k < kmax && k + 1 != EB_SKIP) r = vmul(r, f2s(kap));
-      }
-      g[i] = gc;
-    }
-  }
-}
-
-// Contribution of a pair of objects (centred coordinate xc, weight wt) to the
-// accumulators of the ET edges of a group, in chunks of EB_CHUNK edges outward
-// from the central edge (first upward, then downward).  CHAIN selects the
-// recurrence; otherwise every edge gets its own MUFU.EX2.
+// MUFU.EX2 part of the recurrence for one pair of objects: Gaussian of the
+// central edge and the base / skip ratios.
 template <int ET, bool WEIGHTED, bool CHAIN>
-__device__ __forceinline__ void edges_pair(EdgeAcc* __restrict__ a,
-                                           const GroupConst<ET>& c, float2 xc,
-                                           float2 wt) {
-  constexpr int A0 = ET / 2;
-  constexpr int CH = EB_CHUNK < ET ? EB_CHUNK : ET;
-  constexpr int KU = ET - 1 - A0, KD = A0;  // edges above / below the centre
-  float2 ga = f2s(0.f), ru = f2s(0.f), rd = f2s(0.f), rju = f2s(0.f),
-         rjd = f2s(0.f);
+__device__ __forceinline__ void eb_anchor(const GroupConst<ET>& c, float2 xc,
+                                          float2 wt, EbChain& ch) {
+  typedef EbOrd<ET> OD;
+  ch.ga = ch.ru = ch.rd = ch.rju = ch.rjd = ch.gc = ch.r = f2s(0.f);
   if (CHAIN) {
-    // (the same rounded zs as the one the central edge's chunk uses: all
-    // quantities of an object derive from ONE coordinate per edge)
-    const float2 za = vfma(xc, f2s(-c.ks), f2s(c.cs[A0]));
+    // (the same rounded zs as the one the central edge's accumulations use:
+    // all quantities of an object derive from ONE coordinate per edge)
+    const float2 za = vfma(xc, f2s(-c.ks), f2s(c.cs[OD::A0]));
     const float2 zz = vmul(za, za);
-    ga = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
-    if (WEIGHTED) ga = vmul(ga, wt);
-    if (KU >= 1) {
+    ch.ga = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
+    if (WEIGHTED) ch.ga = vmul(ch.ga, wt);
+    if (OD::KU >= 1) {
       const float2 e = vfma(za, f2s(-c.two_d), f2s(c.nd2));
-      ru = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+      ch.ru = f2(mgb_ex2(e.x), mgb_ex2(e.y));
     }
-    if (KD >= 1) {
+    if (OD::KD >= 1) {
       const float2 e = vfma(za, f2s(c.two_d), f2s(c.nd2));
-      rd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+      ch.rd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
     }
-    if (KU >= EB_SKIP) {
+    if (OD::KU >= EB_SKIP) {
       const float2 e = vfma(za, f2s(-c.two_jd), f2s(c.nj2d2));
-      rju = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+      ch.rju = f2(mgb_ex2(e.x), mgb_ex2(e.y));
     }
-    if (KD >= EB_SKIP) {
+    if (OD::KD >= EB_SKIP) {
       const float2 e = vfma(za, f2s(c.two_jd), f2s(c.nj2d2));
-      rjd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
+      ch.rjd = f2(mgb_ex2(e.x), mgb_ex2(e.y));
     }
   }
-  {
-    float2 gc = ga, r = ru;
+}
+
+// Contribution of NP pairs of objects (centred coordinates xc[], weights
+// wt[]) to the accumulators of the ET edges of a group, in chunks of EB_CHUNK
+// edges in the order of EbOrd.  The MUFU stage of the next chunk (of this pair
+// or the next one) is issued in front of the FMA stage of the current chunk, so
+// that a warp keeps both pipes busy by itself (with three warps per scheduler
+// the bursts of MUFU would otherwise collide and stall the FMA pipe).  CHAIN
+// selects the recurrence; otherwise every edge gets its own MUFU.EX2.
+template <int ET, int NP, bool WEIGHTED, bool CHAIN>
+__device__ __forceinline__ void edges_pairs(EdgeAcc* __restrict__ a,
+                                            const GroupConst<ET>& c,
+                                            const float2* xc,
+                                            const float2* wt) {
+  constexpr int CH = EB_CHUNK < ET ? EB_CHUNK : ET;
+  constexpr int NCH = (ET + CH - 1) / CH;
+  EbChain ch;
+  float2 zs[2][CH], g[2][CH], t[2][CH];
+  eb_anchor<ET, WEIGHTED, CHAIN>(c, xc[0], wt[0], ch);
+  eb_stage_a<ET, CH, WEIGHTED, CHAIN>(c, xc[0], wt[0], 0, ch, zs[0], g[0],
+                                      t[0]);
 #pragma unroll
-    for (int b0 = A0; b0 < ET; b0 += CH) {       // edges b0, b0+1, ...
-      float2 zs[CH], g[CH];
-#pragma unroll
-      for (int i = 0; i < CH; ++i)
-        if (b0 + i < ET) zs[i] = vfma(xc, f2s(-c.ks), f2s(c.cs[b0 + i]));
-      if (CHAIN) {
-        eb_chain<CH>(g, b0 - A0, ET - b0, KU, ga, ru, rju, c.kap, c.kapj, gc,
-                     r);
-      } else {
-#pragma unroll
-        for (int i = 0; i < CH; ++i)
-          if (b0 + i < ET) g[i] = eb_gauss<WEIGHTED>(zs[i], wt);
-      }
-      eb_chunk<CH, WEIGHTED>(a, b0, 1, ET - b0, zs, g, wt);
+  for (int st = 0; st < NP * NCH; ++st) {
+    const int h = st / NCH, n = st - h * NCH;
+    const int nx = st + 1, hx = nx / NCH, nn = nx - hx * NCH;
+    if (nx < NP * NCH) {
+      if (nn == 0) eb_anchor<ET, WEIGHTED, CHAIN>(c, xc[hx], wt[hx], ch);
+      eb_stage_a<ET, CH, WEIGHTED, CHAIN>(c, xc[hx], wt[hx], nn * CH, ch,
+                                          zs[nx & 1], g[nx & 1], t[nx & 1]);
     }
-  }
-  {
-    float2 gc = ga, r = rd;
-#pragma unroll
-    for (int b1 = A0 - 1; b1 >= 0; b1 -= CH) {   // edges b1, b1-1, ...
-      float2 zs[CH], g[CH];
-#pragma unroll
-      for (int i = 0; i < CH; ++i)
-        if (b1 - i >= 0) zs[i] = vfma(xc, f2s(-c.ks), f2s(c.cs[b1 - i]));
-      if (CHAIN) {
-        eb_chain<CH>(g, A0 - b1, b1 + 1, KD, ga, rd, rjd, c.kap, c.kapj, gc,
-                     r);
-      } else {
-#pragma unroll
-        for (int i = 0; i < CH; ++i)
-          if (b1 - i >= 0) g[i] = eb_gauss<WEIGHTED>(zs[i], wt);
-      }
-      eb_chunk<CH, WEIGHTED>(a, b1, -1, b1 + 1, zs, g, wt);
-    }
+    eb_stage_b<ET, CH, WEIGHTED>(a, n * CH, zs[st & 1], g[st & 1], t[st & 1],
+                                 wt[h]);
   }
 }
 
@@ -527,20 +550,33 @@ __device__ __forceinline__ void accumulate_group(
     // central edge (in zs units); zs is monotone in xc
     const bool near = fmaxf(fabsf(fmaf(-c.ks, cmax, c.cs[ET / 2])),
                             fabsf(fmaf(-c.ks, cmin, c.cs[ET / 2]))) <= c.za_lim;
-    // the two pairs of a lane go through the same code one after the other
-    // (not inlined twice: the wide kernels would not fit the instruction
-    // caches)
-    if (__all_sync(0xffffffffu, near)) {
+    // EB_FLAT: both pairs of a lane in one software pipeline (twice the code);
+    // otherwise they go through the same code one after the other
+    const bool chain = __all_sync(0xffffffffu, near);
+#if EB_FLAT
+    {
+      const float2 xcs[2] = {xcA, xcB};
+      const float2 wts[2] = {f2(wv.x, wv.y), f2(wv.z, wv.w)};
+      if (chain) edges_pairs<ET, 2, WEIGHTED, true>(acc, c, xcs, wts);
+      else edges_pairs<ET, 2, WEIGHTED, false>(acc, c, xcs, wts);
+    }
+#else
+    if (chain) {
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h)
-        edges_pair<ET, WEIGHTED, true>(acc, c, h ? xcB : xcA,
-                                       h ? f2(wv.z, wv.w) : f2(wv.x, wv.y));
+      for (int h = 0; h < 2; ++h) {
+        const float2 xc1 = h ? xcB : xcA;
+        const float2 wt1 = h ? f2(wv.z, wv.w) : f2(wv.x, wv.y);
+        edges_pairs<ET, 1, WEIGHTED, true>(acc, c, &xc1, &wt1);
+      }
     } else {
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h)
-        edges_pair<ET, WEIGHTED, false>(acc, c, h ? xcB : xcA,
-                                        h ? f2(wv.z, wv.w) : f2(wv.x, wv.y));
+      for (int h = 0; h < 2; ++h) {
+        const float2 xc1 = h ? xcB : xcA;
+        const float2 wt1 = h ? f2(wv.z, wv.w) : f2(wv.x, wv.y);
+        edges_pairs<ET, 1, WEIGHTED, false>(acc, c, &xc1, &wt1);
+      }
     }
+#endif
   }
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
