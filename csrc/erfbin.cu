@@ -53,6 +53,7 @@
 // [0, batch), the others are only used with batch == 1)
 #define EB_RELAY_WORD 32      // host hand-shake relay (token + parameters)
 #define EB_ABORT_WORD 24      // persistent fit: a step failed, everybody leave
+#define EB_DYN_WORD 8         // + group: tile claim counters of the dynamic tail
 #ifndef EB_HOST_POLL_NS
 #define EB_HOST_POLL_NS 100
 #endif
@@ -488,33 +489,89 @@ __device__ __forceinline__ void eb_fetch(const MgbErfBinModel& md,
   }
 }
 
-// Accumulate the ET edges of a group over the tiles of this CTA that belong
-// to warp `wj` of `wpg` warps in the group; leave the warp-reduced sums
-// (T, O, G, Z per edge) in s_out[4*ET] (lane 0 writes).  `first` holds the
-// warp's first tile, fetched by the caller (in the persistent fit before it
-// waits for the parameters of the step).
+// Tile schedule of a warp.  One tile = 128 consecutive objects.  A group of
+// `wpg` warps per CTA sees every tile once: statically, warp wj of CTA c takes
+// the tiles c + wj*G + j*G*wpg, j = 0, 1, ...  With the dynamic tail only the
+// first ~90% of the tiles are dealt out that way; the rest is claimed two
+// tiles at a time from a per-group counter in device memory, which evens out
+// the few per cent by which the SMs differ in speed (measured: the first and
+// the last CTA of a static split finish 3.3% of the loop time apart).  The
+// price: which warp adds which tail tile varies from run to run, so the fp32
+// partial sums -- not the reduction order, which stays fixed -- and with them
+// the last bits of the results do.  Off = bit-reproducible.
+struct EbSched {
+  int ntiles;              // tiles in the shard (incl. the ragged last one)
+  int per_iter;            // G * wpg: tiles the group consumes per iteration
+  int static_end;          // tiles [0, static_end) are dealt out statically
+  int first;               // this warp's first static tile
+  unsigned* counter;       // claim counter of the group (dynamic tail) or NULL
+};
+
+__device__ __forceinline__ EbSched eb_make_sched(const MgbErfBinModel& md,
+                                                 int wj, int wpg, bool dynamic,
+                                                 unsigned* counter) {
+  EbSched sc;
+  sc.ntiles = (int)(((md.n >> 2) + 32) >> 5);
+  sc.per_iter = (int)gridDim.x * wpg;
+  sc.first = (int)blockIdx.x + wj * (int)gridDim.x;
+  sc.static_end = sc.ntiles;
+  sc.counter = nullptr;
+  if (dynamic) {
+    sc.static_end =
+        (int)(((long long)sc.ntiles * 9 / 10) / sc.per_iter) * sc.per_iter;
+    sc.counter = counter;
+  }
+  return sc;
+}
+
+// Accumulate the ET edges of a group over this warp's tiles (EbSched); leave
+// the warp-reduced sums (T, O, G, Z per edge) in s_out[4*ET] (lane 0 writes).
+// `first` holds the warp's first static tile, fetched by the caller (in the
+// persistent fit before it waits for the parameters of the step).
 template <int ET, bool WEIGHTED>
 __device__ __forceinline__ void accumulate_group(
-    const MgbErfBinModel& md, const GroupConst<ET>& c, float x0, int wj,
-    int wpg, int lane, const EbTile& first, double* s_out) {
+    const MgbErfBinModel& md, const GroupConst<ET>& c, float x0,
+    const EbSched& sc, int lane, const EbTile& first, double* s_out) {
   EdgeAcc acc[ET];
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
     acc[e].T = 0.f; acc[e].O = 0.f;
     acc[e].G = 0.f; acc[e].Z = 0.f;
   }
-  const long long n4 = md.n >> 2;
-  // CTA c owns tiles c, c+G, ...; within the CTA warp wj of the group takes
-  // every wpg-th of them.
-  const long long tstride = (long long)gridDim.x * wpg * 32;
-  long long i0 = ((long long)blockIdx.x + (long long)wj * gridDim.x) * 32;
+  // next tile after `t` (or -1): static stride first, then claims of two
+  // consecutive tiles from the group's counter (warp-uniform)
+  int second = -1;
+  auto advance = [&](int t) -> int {
+    const int t2 = t + sc.per_iter;
+    if (t < sc.static_end && t2 < sc.static_end) return t2;
+    if (sc.counter == nullptr) return -1;
+    if (second >= 0) {
+      const int t3 = second;
+      second = -1;
+      return t3;
+    }
+    unsigned cl = 0;
+    if (lane == 0) cl = atomicAdd(sc.counter, 1u);
+    cl = __shfl_sync(0xffffffffu, cl, 0);
+    const unsigned t3 = (unsigned)sc.static_end + 2u * cl;
+    if (t3 >= (unsigned)sc.ntiles) return -1;
+    second = (t3 + 1u < (unsigned)sc.ntiles) ? (int)t3 + 1 : -1;
+    return (int)t3;
+  };
+  int cur = sc.first;
   EbTile nxt = first;
-  // The trip count is warp-uniform (i0 does not depend on the lane) because the
-  // body votes with __all_sync.  The next tile is fetched before the current
-  // one is consumed (register double buffering hides the DRAM latency).
-  for (; i0 < n4 + 1; i0 += tstride) {
+  if (sc.first >= sc.static_end) {      // no static share: start with a claim
+    cur = advance(sc.static_end);
+    if (cur >= 0) eb_fetch<WEIGHTED>(md, (long long)cur * 32, lane, nxt);
+  }
+  // The trip count is warp-uniform (tile indices do not depend on the lane)
+  // because the body votes with __all_sync.  The next tile is fetched before
+  // the current one is consumed (register double buffering hides the DRAM
+  // latency, and that of the claim).
+  while (cur >= 0) {
     const float4 xv = nxt.x, wv = nxt.w;
-    if (i0 + tstride < n4 + 1) eb_fetch<WEIGHTED>(md, i0 + tstride, lane, nxt);
+    cur = advance(cur);
+    if (cur >= 0) eb_fetch<WEIGHTED>(md, (long long)cur * 32, lane, nxt);
     const float2 xcA = vadd(f2(xv.x, xv.y), f2s(-x0));
     const float2 xcB = vadd(f2(xv.z, xv.w), f2s(-x0));
     // objects for which every edge of this group is saturated contribute
@@ -616,7 +673,7 @@ template <int ET, bool WEIGHTED>
 __device__ __forceinline__ void run_group(const MgbErfBinModel& md,
                                           EbShared& sh, double ks_d,
                                           double width, bool uniform,
-                                          int e_first, int wj, int wpg,
+                                          int e_first, const EbSched& sc,
                                           int warp, int lane,
                                           const EbTile& first) {
   GroupConst<ET> c;
@@ -637,7 +694,7 @@ __device__ __forceinline__ void run_group(const MgbErfBinModel& md,
                        (2.0 * EB_SKIP * d);
     c.za_lim = (float)(lim < (double)EB_ZA_MAX ? lim : (double)EB_ZA_MAX);
   }
-  accumulate_group<ET, WEIGHTED>(md, c, md.x0, wj, wpg, lane, first,
+  accumulate_group<ET, WEIGHTED>(md, c, md.x0, sc, lane, first,
                                  sh.warp[warp]);
 }
 
@@ -670,7 +727,11 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
   const int et = lay.e0[grp + 1] - e_first;
   const int wpg = lay.w0[grp + 1] - lay.w0[grp];
   const int wj = warp - lay.w0[grp];
-  const long long tile0 = ((long long)blockIdx.x + (long long)wj * G) * 32;
+  // dynamic tail (unless MGB_STEP_STATIC_SPLIT): claim counters are words
+  // EB_DYN_WORD + group of the counter block (batch == 1 only)
+  const EbSched sched = eb_make_sched(
+      md, wj, wpg, (a.flags & MGB_STEP_STATIC_SPLIT) == 0 && gridDim.y == 1,
+      counters + EB_DYN_WORD + grp);
 
   // Programmatic dependent launch: this grid may have been scheduled while
   // the previous step's last CTA was still in its epilogue (launch latency and
@@ -759,7 +820,8 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     // flight while this CTA waits for them ------------------------------------
     EbTile first;
     first.w = make_float4(1.f, 1.f, 1.f, 1.f);
-    if (tile0 < (md.n >> 2) + 1) eb_fetch<WEIGHTED>(md, tile0, lane, first);
+    if (sched.first < sched.static_end)
+      eb_fetch<WEIGHTED>(md, (long long)sched.first * 32, lane, first);
 
     if (s > 0) {
       // persistent fit: wait until the elected CTA of the previous step has
@@ -818,10 +880,10 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     // ---- main loop: this warp's edge group -------------------------------------
     if (et == ET_HI) {
       run_group<ET_HI, WEIGHTED>(md, sh, ks_d, lay.width, lay.uniform != 0,
-                                 e_first, wj, wpg, warp, lane, first);
+                                 e_first, sched, warp, lane, first);
     } else {
       run_group<(ET_HI > 1 ? ET_HI - 1 : 1), WEIGHTED>(
-          md, sh, ks_d, lay.width, lay.uniform != 0, e_first, wj, wpg, warp,
+          md, sh, ks_d, lay.width, lay.uniform != 0, e_first, sched, warp,
           lane, first);
     }
     // the object loop of this CTA is done: let the next launch's grid be
@@ -893,11 +955,29 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     __threadfence();
     unsigned long long tr1 = 0, tr2 = 0, tr3 = 0;
     if (a.trace && tid == 0) tr1 = mgb_globaltimer_ns();
+    // optimiser state of parameter `lane` (warp 0): loaded now, consumed after
+    // the reductions -- keeps three dependent L2 round trips out of the
+    // epilogue
+    int o_step = 0;
+    float o_p = 0.f, o_u = 0.f, o_m = 0.f, o_v = 0.f;
+    if (a.mode >= MGB_MODE_ADAM && warp == 0) {
+      o_step = __ldcg(a.opt_step);
+      if (lane < md.nparams) {
+        o_p = __ldcg(a.opt_p + lane);
+        if (a.mode == MGB_MODE_ADAM) {
+          o_u = __ldcg(a.opt_u + lane);
+          o_m = __ldcg(a.opt_m + lane);
+          o_v = __ldcg(a.opt_v + lane);
+        }
+      }
+    }
 
     // ---- fixed-order grid reduction --------------------------------------------
     mgb_grid_reduce_f64(partials + (size_t)b * NC * MP, NC, MP, sh.tot, tid,
                         nthreads);
     if (tid == 0) counters[b] = 0u;  // ready for the next step / launch
+    if (sched.counter != nullptr && tid < lay.ng)
+      counters[EB_DYN_WORD + tid] = 0u;
     __syncthreads();
     if (a.trace && tid == 0) tr2 = mgb_globaltimer_ns();
 
@@ -970,13 +1050,14 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
         if (mine && a.out_grad) a.out_grad[(size_t)b * P + i] = grad;
         if (a.mode >= MGB_MODE_ADAM) {
           // ---- optimiser update (replicated, deterministic on every GPU) ----
-          const int step = __ldcg(a.opt_step);  // updates applied so far
+          const int step = o_step;              // updates applied so far
           const int row = step - a.step_base;   // row of this step
           if (lane == 0 && a.loss_hist && row >= 0 && row < a.traj_rows)
             a.loss_hist[row] = (float)loss;
           if (mine)
-            mgb_opt_update_param(a, i, P, step, row, grad, a.bound_kind[i],
-                                 a.bound_lo[i], a.bound_hi[i]);
+            mgb_opt_update_param_pre(a, i, P, step, row, grad, a.bound_kind[i],
+                                     a.bound_lo[i], a.bound_hi[i], o_p, o_u,
+                                     o_m, o_v);
           __syncwarp();                   // every lane has written its state
           if (lane == 0) {
             if (nsteps > 1) {
@@ -1221,7 +1302,14 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   MGB_REQUIRE(model && args && scratch, MGB_EINVAL,
               "mgb_erfbin_step: null argument");
   const MgbErfBinModel& md = *model;
-  const MgbStepArgs& a = *args;
+  MgbStepArgs a = *args;
+  {
+    static const bool deterministic = [] {
+      const char* e = getenv("MULTIGRAD_B200_DETERMINISTIC");
+      return e && e[0] == '1';
+    }();
+    if (deterministic) a.flags |= MGB_STEP_STATIC_SPLIT;
+  }
   MGB_REQUIRE(md.nbins >= 1 && md.nbins <= MGB_MAX_BINS, MGB_ETOOBIG,
               "mgb_erfbin_step: nbins=%d outside [1,%d]", md.nbins,
               MGB_MAX_BINS);

@@ -46,20 +46,18 @@ __device__ __forceinline__ float mgb_bound_jac(int kind, float lo, float hi,
 // Trajectory convention: GD records the parameters *before* the update in
 // row `row` (util.py:105-110); Adam records the parameters *after* it in row
 // `row + 1` (row 0 is the initial guess, written by the host).
+// The core takes the state of parameter `i` in registers (p, u, m0, v0) so
+// that a caller can have loaded it long before the gradient is known.
 template <class Args>
-__device__ __forceinline__ void mgb_opt_update_param(
+__device__ __forceinline__ void mgb_opt_update_param_pre(
     const Args& a, int i, int P, int step, int row, float grad, int kind,
-    float lo, float hi) {
+    float lo, float hi, float p, float u, float m0, float v0) {
   if (a.mode == MGB_MODE_GD) {
-    const float p = a.opt_p[i];
     if (a.traj && row >= 0 && row < a.traj_rows)
       a.traj[(size_t)row * P + i] = p;
     a.opt_p[i] = p - a.lr * grad;
     return;
   }
-  const float p = a.opt_p[i];
-  float u = a.opt_u[i];
-  const float m0 = a.opt_m[i], v0 = a.opt_v[i];
   const float c1 = 1.0f - powf(a.b1, (float)(step + 1));
   const float c2 = 1.0f - powf(a.b2, (float)(step + 1));
   const float gi = grad * mgb_bound_jac(kind, lo, hi, a.jac_at_params ? p : u);
@@ -74,4 +72,19 @@ __device__ __forceinline__ void mgb_opt_update_param(
   a.opt_p[i] = pn;
   if (a.traj && row + 1 >= 0 && row + 1 < a.traj_rows)
     a.traj[(size_t)(row + 1) * P + i] = pn;
+}
+
+template <class Args>
+__device__ __forceinline__ void mgb_opt_update_param(
+    const Args& a, int i, int P, int step, int row, float grad, int kind,
+    float lo, float hi) {
+  const float p = a.opt_p[i];
+  float u = 0.f, m0 = 0.f, v0 = 0.f;
+  if (a.mode != MGB_MODE_GD) {
+    u = a.opt_u[i];
+    m0 = a.opt_m[i];
+    v0 = a.opt_v[i];
+  }
+  mgb_opt_update_param_pre(a, i, P, step, row, grad, kind, lo, hi, p, u, m0,
+                           v0);
 }

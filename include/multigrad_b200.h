@@ -152,6 +152,15 @@ enum {
   MGB_MODE_GD = 4            /* + fixed-step gradient-descent update         */
 };
 
+/* MgbStepArgs.flags.  By default the last ~10% of the object tiles are handed
+ * out through an atomic counter (evens out the SMs: 2-3% faster); which warp
+ * adds which of those tiles varies, so results differ in the last bits from
+ * run to run (the replicas on different GPUs still agree bit for bit).
+ * STATIC_SPLIT: fully static tile assignment, bit-reproducible results (also
+ * selected for every launch by the environment variable
+ * MULTIGRAD_B200_DETERMINISTIC=1). */
+#define MGB_STEP_STATIC_SPLIT 1
+
 typedef struct MgbStepArgs {
   int32_t mode;
   int32_t batch;            /* B parameter vectors (optimiser modes: 1)      */
@@ -194,7 +203,7 @@ typedef struct MgbStepArgs {
    * compiled lax.scan (multigrad/mpi4jax/multigrad.py:38-58).  0 or 1: one
    * step per launch. */
   int32_t nsteps;
-  int32_t reserved0;
+  int32_t flags;            /* MGB_STEP_* bits                               */
   /* Optional device buffer of %globaltimer stamps (tools/step_trace.py):
    * per step 8 + 2*grid uint64 words; NULL = no tracing. */
   uint64_t* trace;

@@ -57,6 +57,10 @@ class ErfBinnedModel(OnePointModel):
     sigma_link : ``"identity"`` or ``"log10"``
     loss : ``"log_mse"`` | ``"mse"`` | ``"chi2"``;  loss_eps, inv_err
     nparams, mu_index, sigma_index : layout of the parameter vector
+    deterministic : ``True`` = bit-reproducible results from run to run (fully
+        static work split in the kernel, 2-3% slower; also
+        ``MULTIGRAD_B200_DETERMINISTIC=1``).  The replicas on different GPUs
+        agree bit for bit either way.
 
     ``aux_data`` may carry the same information under the reference example's
     keys (``log_halo_masses``, ``smf_bin_edges``, ``volume``,
@@ -74,6 +78,7 @@ class ErfBinnedModel(OnePointModel):
     nparams: int = 2
     mu_index: int = 0
     sigma_index: int = 1
+    deterministic: bool = False
 
     def __post_init__(self):
         super().__post_init__()
@@ -151,6 +156,7 @@ class ErfBinnedModel(OnePointModel):
                 sig_idx=self.sigma_index, sigma_link=self.sigma_link,
                 loss=self.loss, loss_eps=self.loss_eps, weights=self.weights,
                 peer_table=table)
+            self._plan.deterministic = bool(self.deterministic)
             self.x = self._plan.x
         return self._plan
 

@@ -85,7 +85,7 @@ class MgbStepArgs(C.Structure):
         ("bound_hi", C.c_float * MGB_MAX_PARAMS),
         ("wait_flag", C.c_void_p), ("wait_value", C.c_uint32),
         ("wait_timeout_ms", C.c_uint32),
-        ("nsteps", C.c_int32), ("reserved0", C.c_int32),
+        ("nsteps", C.c_int32), ("flags", C.c_int32),
         ("trace", C.c_void_p),
     ]
 
@@ -103,6 +103,7 @@ class MgbGroupArgs(C.Structure):
 
 
 MODE_SUMSTATS, MODE_SUMSTATS_JAC, MODE_LOSS_GRAD, MODE_ADAM, MODE_GD = range(5)
+STEP_STATIC_SPLIT = 1
 
 
 def nvcc_path() -> Optional[str]:

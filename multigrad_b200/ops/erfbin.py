@@ -103,6 +103,10 @@ class ErfBinPlan:
         self.world = peer_table.world if peer_table is not None else 1
         self._scratch = {}
         self._scratch_for(1)
+        # True: fully static tile split, bit-reproducible results (2-3%
+        # slower); also forced by MULTIGRAD_B200_DETERMINISTIC=1 (read by the
+        # library).  See MGB_STEP_STATIC_SPLIT in include/multigrad_b200.h.
+        self.deterministic = False
 
     # ------------------------------------------------------------------ utils
     def set_target(self, target, inv_err=None) -> None:
@@ -129,6 +133,10 @@ class ErfBinPlan:
     def launch(self, args: MgbStepArgs) -> None:
         global _LAUNCHES
         s = self._scratch_for(args.batch)
+        if self.deterministic:
+            args.flags |= _lib.STEP_STATIC_SPLIT
+        else:
+            args.flags &= ~_lib.STEP_STATIC_SPLIT
         if torch.cuda.current_device() != self.device.index:
             torch.cuda.set_device(self.device)     # one process per GPU
         rc = self.lib.mgb_erfbin_step(

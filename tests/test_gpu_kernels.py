@@ -17,6 +17,11 @@ pytestmark = pytest.mark.gpu
 SELF = mg.Comm(None)
 
 
+def erfbin_launches():
+    from multigrad_b200.ops import erfbin
+    return erfbin.launch_count()
+
+
 def dev():
     return torch.device("cuda", 0)
 
@@ -221,13 +226,91 @@ def test_fused_adam_trajectory_matches_generic(bounds, compat):
 
 
 def test_fused_adam_cuda_graph_equals_stream_launches():
-    m, x, w, edges = make(n=20_000, k=10)
+    m, x, w, edges = make(n=20_000, k=10, deterministic=True)
     m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
     a = m.run_adam([-1.7, 0.35], nsteps=130, learning_rate=0.01,
                    use_graph=False)
     b = m.run_adam([-1.7, 0.35], nsteps=130, learning_rate=0.01,
                    use_graph=True)
     assert torch.equal(a, b)            # deterministic reduction order
+
+
+@pytest.mark.parametrize("k", [10, 20])
+def test_persistent_fit_equals_per_step_launches(k, monkeypatch):
+    """One persistent launch of n steps (CTAs stay resident, parameters
+    handed on through device memory) reproduces n single-step launches bit
+    for bit in deterministic mode -- Adam with bounds and plain GD."""
+    m, x, w, edges = make(n=300_000, k=k, deterministic=True)
+    m.set_target(m.calc_sumstats_from_params([-2.0, 0.2]))
+    bounds = [(-3.0, 0.0), (0.05, None)]
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("MULTIGRAD_B200_PERSISTENT", mode)
+        n0 = erfbin_launches()
+        traj, loss = m.run_adam([-1.7, 0.35], nsteps=60, learning_rate=0.01,
+                                param_bounds=bounds, return_loss=True)
+        gd = m.run_simple_grad_descent([-1.9, 0.25], nsteps=25,
+                                       learning_rate=1e-3)
+        torch.cuda.synchronize()
+        out[mode] = (traj.clone(), loss.clone(), gd.params.clone(),
+                     gd.loss.clone(), erfbin_launches() - n0)
+    assert out["0"][4] == 85 and out["1"][4] == 2
+    for a, b in zip(out["0"][:4], out["1"][:4]):
+        assert torch.equal(a, b)
+    assert bool(torch.isfinite(out["1"][0]).all())
+
+
+def test_dynamic_tail_matches_static_split():
+    """Default scheduling (last tenth of the tiles claimed through an atomic
+    counter) against the bit-reproducible static split: same numbers up to
+    fp32 summation order, and the static split repeats itself exactly."""
+    md, x, w, edges = make(n=400_000, k=10)
+    ms, _, _, _ = make(n=400_000, k=10, deterministic=True)
+    p = [-1.8, 0.3]
+    sd, jd = md.calc_sumstats_and_jac_from_params(p)
+    ss, js = ms.calc_sumstats_and_jac_from_params(p)
+    ss2, js2 = ms.calc_sumstats_and_jac_from_params(p)
+    assert torch.equal(ss, ss2) and torch.equal(js, js2)
+    assert torch.allclose(sd, ss, rtol=2e-6)
+    assert torch.allclose(jd, js, rtol=1e-5, atol=2e-6 * float(js.abs().max()))
+    so, dmu, dsg = oracle(x, edges, md._norm64, p)
+    assert torch.allclose(sd.double().cpu(), so, rtol=3e-6, atol=1e-12)
+
+
+def test_non_uniform_edges_take_the_per_edge_path():
+    """Edges that are not uniformly spaced cannot use the Gaussian
+    recurrence; same accuracy through the per-edge path."""
+    n = 50_000
+    g = torch.Generator().manual_seed(5)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    edges = np.array([9.0, 9.05, 9.2, 9.3, 9.55, 9.6, 9.8, 10.0, 10.3])
+    m = ErfBinnedModel(x=x.to(dev()), bin_edges=edges, volume=10.0 * n,
+                       comm=SELF, device=dev())
+    for p in ([-1.8, 0.3], [-1.0, 0.12]):
+        s, jac = m.calc_sumstats_and_jac_from_params(p)
+        so, dmu, dsg = oracle(x, edges, m._norm64, p)
+        assert torch.allclose(s.double().cpu(), so, rtol=3e-6, atol=1e-12)
+        assert torch.allclose(jac[:, 0].double().cpu(), dmu, rtol=1e-5,
+                              atol=3e-6 * float(dmu.abs().max()))
+        assert torch.allclose(jac[:, 1].double().cpu(), dsg, rtol=1e-5,
+                              atol=3e-6 * float(dsg.abs().max()))
+
+
+@pytest.mark.parametrize("sigma", [0.03, 0.08, 0.2, 0.7, 2.5])
+def test_recurrence_and_per_edge_paths_agree(sigma, monkeypatch):
+    """Uniform bins over a range of widths (recurrence on, off by its own
+    accuracy criterion, and forced off): all within the float64 tolerances."""
+    m, x, w, edges = make(n=100_000, k=10)
+    p = [-1.6, sigma]
+    so, dmu, dsg = oracle(x, edges, m._norm64, p)
+    for chain in ("1", "0"):
+        monkeypatch.setenv("MULTIGRAD_B200_CHAIN", chain)
+        s, jac = m.calc_sumstats_and_jac_from_params(p)
+        assert torch.allclose(s.double().cpu(), so, rtol=3e-6, atol=1e-12)
+        assert torch.allclose(jac[:, 0].double().cpu(), dmu, rtol=1e-5,
+                              atol=3e-6 * float(dmu.abs().max()))
+        assert torch.allclose(jac[:, 1].double().cpu(), dsg, rtol=1e-5,
+                              atol=3e-6 * float(dsg.abs().max()))
 
 
 def test_fused_gd_matches_generic():

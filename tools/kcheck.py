@@ -29,7 +29,7 @@ na = 1_000_000
 xa = smf.synthetic_log_halo_masses(na, 0, 1, device=dev)
 edges = np.linspace(9, 10, 11)
 ma = SMFModel(x=xa, bin_edges=edges, volume=10.0 * na, comm=SELF, device=dev,
-              target_sumstats=np.ones(10))
+              target_sumstats=np.ones(10), deterministic=True)
 errs = []
 for p in ([-2.0, 0.2], [-1.0, 0.5], [-1.6, 0.08], [-1.2, 1.5]):
     s, j = ma.calc_sumstats_and_jac_from_params(p)
