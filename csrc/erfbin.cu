@@ -166,9 +166,7 @@ struct EdgeAcc {
 #ifndef EB_CHUNK
 #define EB_CHUNK 3
 #endif
-#ifndef EB_FLAT
-#define EB_FLAT 0
-#endif
+
 
 // warp-uniform constants of one edge group for the current parameters
 template <int ET>
@@ -412,10 +410,10 @@ __device__ __forceinline__ void edges_pairs(EdgeAcc* __restrict__ a,
 #define EB_MIN_CTAS 2
 #endif
 #ifndef EB_TARGET_WARPS
-#define EB_TARGET_WARPS 24
+#define EB_TARGET_WARPS 16
 #endif
 #ifndef EB_MAX_WARPS
-#define EB_MAX_WARPS 12
+#define EB_MAX_WARPS 8
 #endif
 #ifndef EB_WIDE_WARPS
 #define EB_WIDE_WARPS 12
@@ -454,42 +452,52 @@ struct EbLayout {
   int w0[EB_MAX_GROUPS + 1];    // first warp of group g (w0[ng] = nwarps)
 };
 
+// one tile = EB_TILE_F4 runs of 32 consecutive float4 (128 objects for 1):
+// lane `lane` of the warp holds one float4 of every run.  (Two runs per
+// iteration would halve the per-tile bookkeeping -- 10% of the instructions
+// -- but cost 10% through register pressure: measured 723 vs 653 us.)
+#ifndef EB_TILE_F4
+#define EB_TILE_F4 1
+#endif
+#define EB_TILE_OBJS (128 * EB_TILE_F4)
 struct EbTile {
-  float4 x, w;
+  float4 x[EB_TILE_F4], w[EB_TILE_F4];
 };
 
-// one tile = 32 consecutive float4 (128 objects); lane `lane` of the warp
-// fetches its float4 (padding objects beyond the end)
+// fetch tile `tile` (padding objects beyond the end of the shard)
 template <bool WEIGHTED>
-__device__ __forceinline__ void eb_fetch(const MgbErfBinModel& md,
-                                         long long base, int lane, EbTile& t) {
+__device__ __forceinline__ void eb_fetch(const MgbErfBinModel& md, int tile,
+                                         int lane, EbTile& t) {
   const float4* __restrict__ x4 = reinterpret_cast<const float4*>(md.x);
   const float4* __restrict__ w4 = reinterpret_cast<const float4*>(md.w);
   const long long n4 = md.n >> 2;
-  const long long i = base + lane;
-  if (i < n4) {
-    t.x = __ldg(x4 + i);
-    if (WEIGHTED) t.w = __ldg(w4 + i);
-  } else {
-    t.x = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
-                      EB_SENTINEL_X);
-    if (WEIGHTED) t.w = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i == n4) {  // ragged tail: the last n % 4 objects
-      const long long b4 = n4 << 2;
-      const int rem = (int)(md.n - b4);
-      if (rem > 0) t.x.x = md.x[b4];
-      if (rem > 1) t.x.y = md.x[b4 + 1];
-      if (rem > 2) t.x.z = md.x[b4 + 2];
-      if (WEIGHTED) {
-        if (rem > 0) t.w.x = md.w[b4];
-        if (rem > 1) t.w.y = md.w[b4 + 1];
-        if (rem > 2) t.w.z = md.w[b4 + 2];
+#pragma unroll
+  for (int q = 0; q < EB_TILE_F4; ++q) {
+    const long long i = (long long)tile * (32 * EB_TILE_F4) + q * 32 + lane;
+    if (i < n4) {
+      t.x[q] = __ldg(x4 + i);
+      if (WEIGHTED) t.w[q] = __ldg(w4 + i);
+    } else {
+      t.x[q] = make_float4(EB_SENTINEL_X, EB_SENTINEL_X, EB_SENTINEL_X,
+                           EB_SENTINEL_X);
+      if (WEIGHTED) t.w[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i == n4) {  // ragged tail: the last n % 4 objects
+        const long long b4 = n4 << 2;
+        const int rem = (int)(md.n - b4);
+        if (rem > 0) t.x[q].x = md.x[b4];
+        if (rem > 1) t.x[q].y = md.x[b4 + 1];
+        if (rem > 2) t.x[q].z = md.x[b4 + 2];
+        if (WEIGHTED) {
+          if (rem > 0) t.w[q].x = md.w[b4];
+          if (rem > 1) t.w[q].y = md.w[b4 + 1];
+          if (rem > 2) t.w[q].z = md.w[b4 + 2];
+        }
       }
     }
   }
 }
 
-// Tile schedule of a warp.  One tile = 128 consecutive objects.  A group of
+// Tile schedule of a warp (one tile = EB_TILE_OBJS consecutive objects).  A group of
 // `wpg` warps per CTA sees every tile once: statically, warp wj of CTA c takes
 // the tiles c + wj*G + j*G*wpg, j = 0, 1, ...  With the dynamic tail only the
 // first ~90% of the tiles are dealt out that way; the rest is claimed two
@@ -511,7 +519,7 @@ __device__ __forceinline__ EbSched eb_make_sched(const MgbErfBinModel& md,
                                                  int wj, int wpg, bool dynamic,
                                                  unsigned* counter) {
   EbSched sc;
-  sc.ntiles = (int)(((md.n >> 2) + 32) >> 5);
+  sc.ntiles = (int)((md.n >> 2) / (32 * EB_TILE_F4)) + 1;
   sc.per_iter = (int)gridDim.x * wpg;
   sc.first = (int)blockIdx.x + wj * (int)gridDim.x;
   sc.static_end = sc.ntiles;
@@ -562,43 +570,54 @@ __device__ __forceinline__ void accumulate_group(
   EbTile nxt = first;
   if (sc.first >= sc.static_end) {      // no static share: start with a claim
     cur = advance(sc.static_end);
-    if (cur >= 0) eb_fetch<WEIGHTED>(md, (long long)cur * 32, lane, nxt);
+    if (cur >= 0) eb_fetch<WEIGHTED>(md, cur, lane, nxt);
   }
   // The trip count is warp-uniform (tile indices do not depend on the lane)
   // because the body votes with __all_sync.  The next tile is fetched before
   // the current one is consumed (register double buffering hides the DRAM
   // latency, and that of the claim).
   while (cur >= 0) {
-    const float4 xv = nxt.x, wv = nxt.w;
+    const EbTile tl = nxt;
     cur = advance(cur);
-    if (cur >= 0) eb_fetch<WEIGHTED>(md, (long long)cur * 32, lane, nxt);
-    const float2 xcA = vadd(f2(xv.x, xv.y), f2s(-x0));
-    const float2 xcB = vadd(f2(xv.z, xv.w), f2s(-x0));
+    if (cur >= 0) eb_fetch<WEIGHTED>(md, cur, lane, nxt);
+    float2 xcA[EB_TILE_F4], xcB[EB_TILE_F4];
+    float cmin = 3.0e38f, cmax = -3.0e38f;
+#pragma unroll
+    for (int q = 0; q < EB_TILE_F4; ++q) {
+      xcA[q] = vadd(f2(tl.x[q].x, tl.x[q].y), f2s(-x0));
+      xcB[q] = vadd(f2(tl.x[q].z, tl.x[q].w), f2s(-x0));
+      cmin = fminf(fminf(cmin, fminf(xcA[q].x, xcA[q].y)),
+                   fminf(xcB[q].x, xcB[q].y));
+      cmax = fmaxf(fmaxf(cmax, fmaxf(xcA[q].x, xcA[q].y)),
+                   fmaxf(xcB[q].x, xcB[q].y));
+    }
     // objects for which every edge of this group is saturated contribute
     // nothing to any difference between edges: skip them warp-uniformly
-    const float cmin = fminf(fminf(xcA.x, xcA.y), fminf(xcB.x, xcB.y));
-    const float cmax = fmaxf(fmaxf(xcA.x, xcA.y), fmaxf(xcB.x, xcB.y));
     const bool far = (fmaf(-c.ks, cmax, c.cs[0]) > EB_ZS_SKIP) ||
                      (fmaf(-c.ks, cmin, c.cs[ET - 1]) < -EB_ZS_SKIP);
     if (__all_sync(0xffffffffu, far)) {
       // A skipped lane still has to keep the hard counts consistent with the
       // other edge groups, for which the same objects may not be saturated.
       if (WEIGHTED) {
-        // O = weight of objects at or above the edge: all four objects of a
-        // lane that is saturated on the high side (padding has weight 0)
+        // O = weight of objects at or above the edge: all objects of a lane
+        // that is saturated on the high side (padding has weight 0)
         if (fmaf(-c.ks, cmax, c.cs[0]) > EB_ZS_SKIP) {
-          const float cnt = (wv.x + wv.y) + (wv.z + wv.w);
+          float cnt = 0.f;
+#pragma unroll
+          for (int q = 0; q < EB_TILE_F4; ++q)
+            cnt += (tl.w[q].x + tl.w[q].y) + (tl.w[q].z + tl.w[q].w);
 #pragma unroll
           for (int e = 0; e < ET; ++e) acc[e].O += cnt;
         }
       } else {
-        // O = number of objects below the edge: all four objects of a lane
+        // O = number of objects below the edge: all objects of a lane
         // saturated on the low side (padding objects sit there too, in every
         // group alike, so they cancel in the differences between edges)
         if (fmaf(-c.ks, cmin, c.cs[ET - 1]) < -EB_ZS_SKIP) {
 #pragma unroll
           for (int e = 0; e < ET; ++e)
-            acc[e].O = __int_as_float(__float_as_int(acc[e].O) + 4);
+            acc[e].O =
+                __int_as_float(__float_as_int(acc[e].O) + 4 * EB_TILE_F4);
         }
       }
       continue;
@@ -607,33 +626,24 @@ __device__ __forceinline__ void accumulate_group(
     // central edge (in zs units); zs is monotone in xc
     const bool near = fmaxf(fabsf(fmaf(-c.ks, cmax, c.cs[ET / 2])),
                             fabsf(fmaf(-c.ks, cmin, c.cs[ET / 2]))) <= c.za_lim;
-    // EB_FLAT: both pairs of a lane in one software pipeline (twice the code);
-    // otherwise they go through the same code one after the other
     const bool chain = __all_sync(0xffffffffu, near);
-#if EB_FLAT
-    {
-      const float2 xcs[2] = {xcA, xcB};
-      const float2 wts[2] = {f2(wv.x, wv.y), f2(wv.z, wv.w)};
-      if (chain) edges_pairs<ET, 2, WEIGHTED, true>(acc, c, xcs, wts);
-      else edges_pairs<ET, 2, WEIGHTED, false>(acc, c, xcs, wts);
-    }
-#else
-    if (chain) {
+    // the 2*EB_TILE_F4 pairs of a lane go through the same code one after the
+    // other (not inlined several times: the wide kernels would not fit the
+    // instruction caches)
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        const float2 xc1 = h ? xcB : xcA;
-        const float2 wt1 = h ? f2(wv.z, wv.w) : f2(wv.x, wv.y);
-        edges_pairs<ET, 1, WEIGHTED, true>(acc, c, &xc1, &wt1);
+    for (int h = 0; h < 2 * EB_TILE_F4; ++h) {
+      float2 xc1 = (h & 1) ? xcB[0] : xcA[0];
+      float2 wt1 = (h & 1) ? f2(tl.w[0].z, tl.w[0].w) : f2(tl.w[0].x, tl.w[0].y);
+#pragma unroll
+      for (int q = 1; q < EB_TILE_F4; ++q) {
+        if ((h >> 1) == q) {
+          xc1 = (h & 1) ? xcB[q] : xcA[q];
+          wt1 = (h & 1) ? f2(tl.w[q].z, tl.w[q].w) : f2(tl.w[q].x, tl.w[q].y);
+        }
       }
-    } else {
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        const float2 xc1 = h ? xcB : xcA;
-        const float2 wt1 = h ? f2(wv.z, wv.w) : f2(wv.x, wv.y);
-        edges_pairs<ET, 1, WEIGHTED, false>(acc, c, &xc1, &wt1);
-      }
+      if (chain) edges_pairs<ET, 1, WEIGHTED, true>(acc, c, &xc1, &wt1);
+      else edges_pairs<ET, 1, WEIGHTED, false>(acc, c, &xc1, &wt1);
     }
-#endif
   }
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
@@ -819,9 +829,11 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     // ---- first tile of the step: independent of the parameters, so it is in
     // flight while this CTA waits for them ------------------------------------
     EbTile first;
-    first.w = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+    for (int q = 0; q < EB_TILE_F4; ++q)
+      first.w[q] = make_float4(1.f, 1.f, 1.f, 1.f);
     if (sched.first < sched.static_end)
-      eb_fetch<WEIGHTED>(md, (long long)sched.first * 32, lane, first);
+      eb_fetch<WEIGHTED>(md, sched.first, lane, first);
 
     if (s > 0) {
       // persistent fit: wait until the elected CTA of the previous step has
@@ -1189,7 +1201,7 @@ int grid_for(int nbins) {
   int et_hi = 0;
   const int nwarps = make_layout(tmp, &et_hi).nwarps;
   int per_sm = EB_TARGET_WARPS / nwarps;
-  const int cap = et_hi > EB_ET_NARROW ? EB_WIDE_CTAS : 8;
+  const int cap = et_hi > EB_ET_NARROW ? EB_WIDE_CTAS : EB_MIN_CTAS;
   if (per_sm < 1) per_sm = 1;
   if (per_sm > cap) per_sm = cap;
   return sm_count() * per_sm;
