@@ -33,7 +33,52 @@ from ..ops import reference as _ref
 from ..parallel.collectives import reduce_sum
 from ..util import GradDescentResult
 
-__all__ = ["ErfBinnedModel", "SMFModel"]
+__all__ = ["ErfBinnedModel", "SMFModel", "AdamFit"]
+
+
+class AdamFit:
+    """Handle of a device-resident Adam fit (see
+    :meth:`ErfBinnedModel.adam_fit`).  Parameters, moments, trajectory and
+    loss history live on the GPU and are written by the fused kernel; nothing
+    here synchronises with the device."""
+
+    def __init__(self, model, plan, state, args, step0, nsteps):
+        self.model, self._plan, self._st, self._args = model, plan, state, args
+        self._step0, self.nsteps, self.done = step0, nsteps, 0
+
+    def step(self, n: int = 1, use_graph=None) -> "AdamFit":
+        """Enqueue the next ``n`` optimiser steps on the current stream."""
+        n = int(n)
+        if n < 0 or self.done + n > self.nsteps:
+            raise ValueError(f"fit has room for {self.nsteps} steps, "
+                             f"{self.done} done, {n} more asked for")
+        if n == 1:
+            self._args.nsteps = 1
+            self._plan.launch(self._args)
+        elif n > 1:
+            self.model._run_steps(self._plan, self._args, n, use_graph)
+        self.done += n
+        return self
+
+    @property
+    def trajectory(self) -> torch.Tensor:
+        """``(nsteps+1, ndim)``; rows ``0..done`` are valid."""
+        return self._st.traj
+
+    @property
+    def losses(self) -> torch.Tensor:
+        """Loss at the start of every completed step, ``(done,)``."""
+        return self._st.loss_hist[:self.done]
+
+    @property
+    def params(self) -> torch.Tensor:
+        """Current parameters (CUDA tensor, updated in place by the kernel)."""
+        return self._st.p
+
+    @property
+    def state(self):
+        return _adam.AdamState(self._step0 + self.done, self._st.m,
+                               self._st.v)
 
 
 def _np(v):
@@ -114,6 +159,9 @@ class ErfBinnedModel(OnePointModel):
         self._inv_err_t = None
         self._builtin_loss = (type(self).calc_loss_from_sumstats
                               is ErfBinnedModel.calc_loss_from_sumstats)
+        self._builtin_sumstats = (
+            type(self).calc_partial_sumstats_from_params
+            is ErfBinnedModel.calc_partial_sumstats_from_params)
         self._plan = None
         self._host = None
         if self.target_sumstats is not None:
@@ -122,8 +170,12 @@ class ErfBinnedModel(OnePointModel):
     # ------------------------------------------------------------------ setup
     @property
     def fused(self) -> bool:
-        """True when the CUDA kernels are the execution path."""
-        return self.device.type == "cuda"
+        """True when the CUDA kernels are the execution path: CUDA device and
+        the built-in statistic (a subclass that overrides
+        ``calc_partial_sumstats_from_params`` is evaluated by the generic
+        autograd path of :class:`OnePointModel`, never silently by the
+        built-in kernel)."""
+        return self.device.type == "cuda" and self._builtin_sumstats
 
     def set_target(self, target, inv_err=None) -> None:
         """(Re)define the target summary statistics of the built-in loss."""
@@ -327,7 +379,8 @@ class ErfBinnedModel(OnePointModel):
         import ctypes as C
         plan = self.plan()
         P = self.nparams
-        self.loss_and_grad_host(_np(guess).ravel())     # buffers + warm-up
+        if self._host is None:
+            self.loss_and_grad_host(_np(guess).ravel())     # pinned buffers
         h = self._host
         h[5][:] = _np(guess).ravel()
         step0 = 0
@@ -412,12 +465,48 @@ class ErfBinnedModel(OnePointModel):
         """Adam with one fused kernel launch per step (``csrc/erfbin.cu``
         mode 3): sumstats + Jacobian + NVLink all-reduce + loss + chain rule +
         bound transforms + update, trajectory and loss history written on the
-        device.  Same return convention as :meth:`OnePointModel.run_adam`."""
+        device.  Same return convention as :meth:`OnePointModel.run_adam`.
+        ``randkey`` / ``const_randkey`` are validated like the reference does
+        (``multigrad/multigrad.py:291-297``) but have no effect here: the
+        built-in link draws no random numbers (a stochastic link is written
+        with :class:`~multigrad_b200.models.LinkedBinnedModel`, whose kernel
+        derives a ``(seed, step)`` key on the device)."""
+        if const_randkey and randkey is None:
+            raise ValueError("const_randkey=True requires a randkey")
+        if randkey is not None:
+            from ..utils import rng as _rng
+            _rng.init_randkey(randkey)          # type check, as the reference
         if not (self.fused and self._builtin_loss):
             return super().run_adam(
                 guess, nsteps, param_bounds, learning_rate, randkey,
                 const_randkey, comm, reference_compat, init_state,
                 return_state, return_loss)
+        fit = self.adam_fit(guess, nsteps, param_bounds, learning_rate,
+                            reference_compat=reference_compat,
+                            init_state=init_state)
+        fit.step(nsteps, use_graph=use_graph)
+        self._check_peers()
+        out = [fit.trajectory]
+        if return_loss:
+            out.append(fit.losses)
+        if return_state:
+            out.append(fit.state)
+        return out[0] if len(out) == 1 else tuple(out)
+
+    def adam_fit(self, guess, nsteps=100, param_bounds=None,
+                 learning_rate=0.01, reference_compat=True, init_state=None):
+        """Device-resident Adam fit that the caller advances: returns an
+        :class:`AdamFit` with room for ``nsteps`` steps; ``fit.step(n)``
+        enqueues the next ``n`` of them (``n == 1``: one fused launch, ``n >
+        1``: one persistent launch) and returns immediately, so the caller can
+        interleave its own stream work -- logging, a cache flush for a
+        benchmark, an early-stopping test on ``fit.losses`` -- between steps.
+        ``run_adam(guess, nsteps)`` is ``fit.step(nsteps)`` + the results.
+        CUDA + built-in loss only (``None`` otherwise)."""
+        if not (self.fused and self._builtin_loss):
+            return None
+        if self._target_t is None:
+            raise ValueError("no target_sumstats given")
         from ..ops.erfbin import FitState, MODE_ADAM
         plan = self.plan()
         p0 = self._params(guess)
@@ -434,14 +523,7 @@ class ErfBinnedModel(OnePointModel):
         args = plan.make_optimizer_args(
             MODE_ADAM, st, learning_rate, bounds,
             jac_at_params=reference_compat)
-        self._run_steps(plan, args, nsteps, use_graph)
-        self._check_peers()
-        out = [st.traj]
-        if return_loss:
-            out.append(st.loss_hist[:nsteps])
-        if return_state:
-            out.append(_adam.AdamState(step0 + nsteps, st.m, st.v))
-        return out[0] if len(out) == 1 else tuple(out)
+        return AdamFit(self, plan, st, args, step0, int(nsteps))
 
     def run_simple_grad_descent(self, guess, nsteps=100, learning_rate=0.01,
                                 use_graph=None):

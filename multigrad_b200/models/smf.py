@@ -21,7 +21,8 @@ from ..parallel import comm as _comm
 
 __all__ = ["ParamTuple", "load_halo_masses", "load_halo_masses_tutorial",
            "calc_smf_cdf", "calc_smf_bin", "MySMFModel", "TutorialSMFModel",
-           "TARGET_SUMSTATS_TEST", "make_smf_data", "synthetic_log_halo_masses"]
+           "TARGET_SUMSTATS_TEST", "make_smf_data", "synthetic_log_halo_masses",
+           "synthetic_sumstats_and_jac", "synthetic_adam_oracle"]
 
 
 class ParamTuple(NamedTuple):
@@ -143,3 +144,79 @@ def make_smf_data(num_halos=10_000, comm=None, device="cpu"):
         volume=10.0 * num_halos,
         target_sumstats=torch.tensor(TARGET_SUMSTATS_TEST).to(device),
     )
+
+
+# ---------------------------------------------------------------------------
+# float64 oracle for the synthetic catalogue without touching its objects.
+# ``synthetic_log_halo_masses`` places object i at x(q_i), q_i = i*qmax/(N-1):
+# a sum over the objects of a smooth function is the trapezoid sum of
+# f(x(q)), which Gauss-Legendre quadrature plus the Euler-Maclaurin end
+# corrections reproduces to ~1e-12 relative -- the check ``bench.py`` runs at
+# every GPU count against the fused kernels' trajectories.
+# ---------------------------------------------------------------------------
+def synthetic_sumstats_and_jac(num_halos, bin_edges, volume, params,
+                               qmax=0.95, panels=4000, order=8):
+    """``(s[K], ds/dmu[K], ds/dsigma[K])`` in float64 for the model
+    ``mu = x + params[0]``, ``sigma = params[1]`` on the synthetic catalogue
+    of ``num_halos`` objects (sum over ALL objects, i.e. all ranks)."""
+    from scipy.special import erf
+    edges = np.asarray(bin_edges, dtype=np.float64)
+    p_mu, sig = float(params[0]), float(params[1])
+    N = int(num_halos)
+    h = qmax / max(N - 1, 1)
+    xs, ws = np.polynomial.legendre.leggauss(order)
+    bounds = np.linspace(0.0, qmax, panels + 1)
+    half = 0.5 * np.diff(bounds)
+    q = (0.5 * (bounds[1:] + bounds[:-1]))[:, None] + half[:, None] * xs
+    wq = (half[:, None] * ws[None, :]).ravel()
+    q = q.ravel()
+
+    def terms(qv):
+        x = 10.0 - np.log10(1.0 - qv)
+        z = (edges[:, None] - (x + p_mu)[None, :]) / (math.sqrt(2.0) * sig)
+        cdf = 0.5 * (1.0 + erf(z))
+        g = np.exp(-z * z) / math.sqrt(math.pi)
+        return cdf, -g / (math.sqrt(2.0) * sig), -g * z / sig
+
+    def dterms(qv, eps=1e-6):
+        a = terms(np.asarray([min(qv + eps, qmax)]))
+        b = terms(np.asarray([max(qv - eps, 0.0)]))
+        span = min(qv + eps, qmax) - max(qv - eps, 0.0)
+        return [(u - v)[:, 0] / span for u, v in zip(a, b)]
+
+    mid = terms(q)
+    end0 = terms(np.asarray([0.0]))
+    end1 = terms(np.asarray([qmax]))
+    d0, d1 = dterms(0.0), dterms(qmax)
+    out = []
+    for k in range(3):
+        tot = (mid[k] * wq[None, :]).sum(axis=1) / h
+        tot += 0.5 * (end0[k][:, 0] + end1[k][:, 0])
+        tot += (h / 12.0) * (d1[k] - d0[k])
+        out.append(np.diff(tot) / (float(volume) * np.diff(edges)))
+    return tuple(out)
+
+
+def synthetic_adam_oracle(num_halos, bin_edges, volume, target, guess, nsteps,
+                          learning_rate=0.01, b1=0.9, b2=0.999, eps=1e-8):
+    """float64 Adam trajectory ``(nsteps+1, 2)`` and loss history of the
+    log-MSE SMF fit on the synthetic catalogue (unbounded parameters)."""
+    p = np.asarray(guess, dtype=np.float64).copy()
+    tgt = np.asarray(target, dtype=np.float64)
+    m = np.zeros(2)
+    v = np.zeros(2)
+    traj, losses = [p.copy()], []
+    K = tgt.size
+    for i in range(nsteps):
+        s, dmu, dsg = synthetic_sumstats_and_jac(num_halos, bin_edges, volume,
+                                                 p)
+        r = np.log10(s) - np.log10(tgt)
+        losses.append(float(np.mean(r * r)))
+        dl = 2.0 * r / (K * s * math.log(10.0))
+        g = np.array([dl @ dmu, dl @ dsg])
+        m = (1 - b1) * g + b1 * m
+        v = (1 - b2) * g * g + b2 * v
+        mh, vh = m / (1 - b1 ** (i + 1)), v / (1 - b2 ** (i + 1))
+        p = p - learning_rate * mh / (np.sqrt(vh) + eps)
+        traj.append(p.copy())
+    return np.asarray(traj), np.asarray(losses)
