@@ -336,22 +336,38 @@ def gpu_fused_step_uses_one_launch():
         return
     from multigrad_b200.ops import erfbin, allreduce as ar
     data = _data(40_000)
-    model = SMFModel(aux_data=data)
+    model = SMFModel(aux_data=data, deterministic=True)
     model.run_adam([-1.9, 0.3], nsteps=2)       # builds plan + workspace
     e0, a0 = erfbin.launch_count(), ar.launch_count()
     ep0 = COMM.workspace().epoch
     traj, losses = model.run_adam([-1.9, 0.3], nsteps=20, learning_rate=0.01,
                                   return_loss=True)
     torch.cuda.synchronize()
-    assert erfbin.launch_count() - e0 == 20 and ar.launch_count() == a0
+    # ONE persistent launch runs the 20 steps, exchanging once per step
+    assert erfbin.launch_count() - e0 == 1 and ar.launch_count() == a0
     if SIZE > 1:
         assert COMM.workspace().epoch - ep0 == 20   # one exchange per step
     assert bool(torch.isfinite(traj).all()) and losses[-1] < losses[0]
+    # per-step launches through the stepping API: same bits
+    fit = model.adam_fit([-1.9, 0.3], nsteps=20, learning_rate=0.01)
+    e1 = erfbin.launch_count()
+    for _ in range(20):
+        fit.step()
+    torch.cuda.synchronize()
+    assert erfbin.launch_count() - e1 == 20 and ar.launch_count() == a0
+    assert torch.equal(fit.trajectory, traj)
+    assert torch.equal(fit.losses, losses)
     tg = model.run_adam([-1.9, 0.3], nsteps=120, learning_rate=0.01,
                         use_graph=True)
     ts = model.run_adam([-1.9, 0.3], nsteps=120, learning_rate=0.01,
                         use_graph=False)
     assert torch.equal(tg, ts)
+    # default scheduling (dynamic tail): replicas still agree bit for bit
+    md = SMFModel(aux_data=data)
+    td = md.run_adam([-1.9, 0.3], nsteps=60, learning_rate=0.01)
+    assert torch.allclose(td, ts[:61], rtol=1e-5, atol=2e-6)
+    blobs = COMM.allgather(td.cpu().numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
     # host-driven Adam (state on the host): same trajectory on every rank
     th = model.run_adam_host([-1.9, 0.3], nsteps=25, learning_rate=0.01)
     assert torch.allclose(th, ts[:26].cpu(), rtol=1e-5, atol=2e-6)
