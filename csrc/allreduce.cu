@@ -91,10 +91,22 @@ ll_bcast_kernel(const MgbPeerTable pt, float* __restrict__ data, int n,
                      ((unsigned long long)epoch << 32) |
                          __float_as_uint(data[u]));
     }
+    // back-pressure: a broadcast is one-way, so without this the root could
+    // run two broadcasts ahead and overwrite a parity slot that a slow
+    // receiver has not read yet.  Every receiver acknowledges (one tagged
+    // word into the root's slot [parity][receiver][0]); the root leaves only
+    // when all have.
+    for (int s = tid; s < W; s += nt)
+      if (s != root)
+        (void)mgb_ll_wait(pt, mgb_ll_slot(pt, root, parity, s, 0u), epoch);
   } else {
     for (int j = tid; j < n; j += nt)
       data[j] = __uint_as_float(mgb_ll_wait(
           pt, mgb_ll_slot(pt, pt.rank, parity, root, (unsigned)j), epoch));
+    __syncthreads();
+    if (tid == 0)
+      mgb_st_sys_u64(mgb_ll_slot(pt, root, parity, pt.rank, 0u),
+                     (unsigned long long)epoch << 32);
   }
   __syncthreads();
   if (tid == 0) mgb_st_sys_u32(ctrl + MGB_CTRL_EPOCH, epoch);

@@ -1862,71 +1862,3 @@ extern "C" int mgb_erfbin_host_session(
   __sync_synchronize();
   return MGB_OK;
 }
-
-// Root side of one multi-GPU L-BFGS-B evaluation in ONE native call (K6):
-// gate + parameters (pinned host) -> device control block, LL broadcast of the
-// block to the workers' GPUs over NVLink, gated fused loss+gradient launch
-// whose results land directly in pinned host memory (zero copy), poll.
-// ctl_host / ctl_dev hold 1 + P floats (gate, params); with gate == 0 the
-// launch is a no-op on every rank and nothing is waited for (exit blocks).
-// Reference counterpart: the two pickled broadcasts + host-staged reductions
-// per evaluation of multigrad/bfgs.py:72-77.
-extern "C" int mgb_erfbin_bfgs_root_eval(
-    const MgbErfBinModel* model, const MgbPeerTable* pt, const float* ctl_host,
-    float* ctl_dev, float* out_host, void* scratch, uint64_t scratch_bytes,
-    void* stream, uint32_t timeout_ms) {
-  MGB_REQUIRE(model && pt && ctl_host && ctl_dev && out_host, MGB_EINVAL,
-              "mgb_erfbin_bfgs_root_eval: null argument");
-  const int P = model->nparams;
-  MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
-              "mgb_erfbin_bfgs_root_eval: nparams=%d outside [1,%d]", P,
-              MGB_MAX_PARAMS);
-  cudaStream_t st = (cudaStream_t)stream;
-  const bool live = ctl_host[0] != 0.0f;
-  const uint32_t kSentinel = 0x7fc0deadu;
-  volatile uint32_t* o = reinterpret_cast<volatile uint32_t*>(out_host);
-  if (live) {
-    for (int i = 0; i <= P; ++i) o[i] = kSentinel;
-    __sync_synchronize();
-  }
-  MGB_CUDA_CHECK(cudaMemcpyAsync(ctl_dev, ctl_host, sizeof(float) * (1 + P),
-                                 cudaMemcpyHostToDevice, st));
-  int rc = mgb_bcast_f32(pt, ctl_dev, (uint32_t)(1 + P), 0, stream);
-  if (rc != MGB_OK) return rc;
-  MgbStepArgs a;
-  memset(&a, 0, sizeof(a));
-  a.mode = MGB_MODE_LOSS_GRAD;
-  a.batch = 1;
-  a.reduce = pt->world > 1 ? 1 : 0;
-  a.gate = ctl_dev;
-  a.params = ctl_dev + 1;
-  a.out_loss = out_host;
-  a.out_grad = out_host + 1;
-  rc = mgb_erfbin_step(model, &a, pt, scratch, scratch_bytes, stream);
-  if (rc != MGB_OK || !live) return rc;
-  struct timespec t0;
-  clock_gettime(CLOCK_MONOTONIC, &t0);
-  for (unsigned spin = 0;; ++spin) {
-    bool done = true;
-    for (int i = 0; i <= P; ++i) done = done && (o[i] != kSentinel);
-    if (done) break;
-    if ((spin & 0x3ffu) == 0x3ffu) {
-      struct timespec t1;
-      clock_gettime(CLOCK_MONOTONIC, &t1);
-      const double ms = (t1.tv_sec - t0.tv_sec) * 1e3 +
-                        (t1.tv_nsec - t0.tv_nsec) * 1e-6;
-      if (ms > (double)timeout_ms) {
-        const cudaError_t e = cudaStreamQuery(st);
-        if (e != cudaSuccess && e != cudaErrorNotReady) MGB_CUDA_CHECK(e);
-        mgb_set_error("mgb_erfbin_bfgs_root_eval: no result after %u ms",
-                      timeout_ms);
-        return MGB_ESTATE;
-      }
-    }
-#if defined(__x86_64__)
-    __builtin_ia32_pause();
-#endif
-  }
-  __sync_synchronize();
-  return MGB_OK;
-}

@@ -104,9 +104,11 @@ int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc, void* mc,
                            uint64_t mc_bytes, float* data, uint64_t n,
                            void* stream);
 
-/* push `n` floats from `root` to every rank (K6, BFGS parameter hand-off;
- * replaces the pickled "compute"/params bcast of multigrad/bfgs.py:72-77).
- * Non-root ranks wait on the GPU until the data arrives. */
+/* push `n` floats from `root` to every rank over NVLink (replaces a pickled
+ * parameter bcast like multigrad/bfgs.py:72-77 or mpi4jax.bcast,
+ * multigrad/mpi4jax/multigrad.py:52).  Non-root ranks wait on the GPU until
+ * the data arrives and acknowledge; the root returns once every rank has, so
+ * back-to-back broadcasts cannot overrun a slow receiver. */
 int mgb_bcast_f32(const MgbPeerTable* pt, float* data, uint32_t n, int root,
                   void* stream);
 
@@ -249,17 +251,6 @@ int mgb_erfbin_host_session(const MgbErfBinModel* model,
                             float* out_host, void* scratch,
                             uint64_t scratch_bytes, void* stream,
                             uint32_t timeout_ms, int32_t op, uint32_t* seq);
-/* Root side of one multi-GPU L-BFGS-B evaluation (K6) in one call: control
- * block (gate, params; pinned host) -> device, LL broadcast to the workers,
- * gated fused launch writing (loss, grad) into pinned out_host, poll.  With
- * gate == 0 nothing is waited for (the exit blocks that drain the workers'
- * queued launches).  Replaces the pickled broadcasts of
- * multigrad/bfgs.py:72-77. */
-int mgb_erfbin_bfgs_root_eval(const MgbErfBinModel* model,
-                              const MgbPeerTable* pt, const float* ctl_host,
-                              float* ctl_dev, float* out_host, void* scratch,
-                              uint64_t scratch_bytes, void* stream,
-                              uint32_t timeout_ms);
 #define MGB_HOST_FLAG_WORD 16  /* out_host needs MGB_HOST_FLAG_WORD + 1 words */
 int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
                          float* params_host, float* out_host, float* m,

@@ -1,16 +1,25 @@
-"""K6: multi-GPU L-BFGS-B with a device-side control plane.
+"""K6: multi-GPU L-BFGS-B without a control plane.
 
-The reference drives its workers with two pickled MPI broadcasts per
-loss+gradient evaluation (``"compute"`` + params) and a final ``"exit"``
-(``multigrad/bfgs.py:72-106``).  Here the root's parameters reach the other
-GPUs by NVLink stores issued from a kernel (``mgb_bcast_f32``) and the
-workers *wait on the GPU*: each worker keeps ``DEPTH`` (hand-off, evaluation)
-kernel pairs queued, so by the time the root pushes the next point the
-worker's kernels are already resident and the evaluation starts within one
-NVLink latency.  The first float of the pushed block is a gate: 1 = evaluate,
-0 = exit (the evaluation kernel turns into a no-op).  The root sends exactly
-``DEPTH`` exit blocks so that every queued pair drains and all ranks execute
-the same number of collectives.
+The reference runs scipy's L-BFGS-B on rank 0 and drives the other ranks with
+two pickled MPI broadcasts per loss+gradient evaluation (``"compute"`` +
+params) plus an ``"exit"`` and a broadcast of the result object
+(``multigrad/bfgs.py:72-111``).
+
+Here the fused evaluation leaves *bit-identical* loss and gradient on every
+rank (rank-ordered NVLink sum inside the kernel), so -- exactly as for Adam --
+every rank can run the same deterministic optimiser on its own copy: scipy's
+L-BFGS-B is a serial float64 code, identical inputs give identical iterates on
+every rank.  Each rank therefore drives its own GPU through an *evaluation
+session* (``mgb_erfbin_host_session``: one grid always pre-launched and
+waiting on the GPU for the next parameters in pinned host memory, results
+written straight back into pinned host memory), and the only thing that
+crosses GPUs is the 3K-double exchange inside the evaluation kernel.  No
+parameter hand-off, no exit message, no result broadcast: one evaluation costs
+the kernel plus the optimiser's own host time, at every GPU count.
+
+The ranks verify afterwards that they really did the same thing (evaluation
+count and final iterate, one cold allgather); a disagreement -- which would
+mean a non-deterministic host optimiser -- raises on every rank.
 """
 from __future__ import annotations
 
@@ -19,10 +28,6 @@ import scipy.optimize
 import torch
 
 from .. import util
-from ..ops import _lib
-from ..ops.allreduce import bcast_
-
-DEPTH = 4
 
 
 def _np64(v):
@@ -31,104 +36,62 @@ def _np64(v):
     return np.asarray(v, dtype=np.float64)
 
 
-def run_bfgs_device(model, guess, maxsteps, param_bounds, comm):
-    from ..ops.erfbin import MODE_LOSS_GRAD
-    plan = model.plan()
-    P = model.nparams
-    dev = model.device
+def run_bfgs_replicated(model, guess, maxsteps, param_bounds, comm,
+                        _before_eval=None):
+    """L-BFGS-B on every rank of ``comm`` over a device evaluation session of
+    ``model`` (see the module docstring).  ``_before_eval`` is a test hook
+    called in front of every evaluation (rank-skew injection)."""
     if param_bounds is not None and hasattr(param_bounds, "tolist"):
         param_bounds = param_bounds.tolist()
-    ctl = torch.zeros(1 + P, dtype=torch.float32, device=dev)
-    d_out = torch.zeros(1 + P, dtype=torch.float32, device=dev)
-    a = _lib.MgbStepArgs()
-    a.mode, a.batch, a.reduce = MODE_LOSS_GRAD, 1, 1
-    a.gate = ctl.data_ptr()
-    a.params = ctl.data_ptr() + 4
-    a.out_loss = d_out.data_ptr()
-    a.out_grad = d_out.data_ptr() + 4
-    stream = torch.cuda.current_stream(dev)
+    x0 = _np64(guess).ravel()
+    pbar = util.trange(maxsteps, desc="BFGS Gradient Descent Progress",
+                       leave=True)
 
-    if comm.rank == 0:
-        import ctypes as C
-        h_in = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
-        h_out = torch.zeros(1 + P, dtype=torch.float32).pin_memory()
-        n_in, n_out = h_in.numpy(), h_out.numpy()
-        scratch = plan._scratch_for(1)
-        timeout = max(60000, 2 * int(plan.pt.spin_timeout_ms))
-        if torch.cuda.current_device() != dev.index:
-            torch.cuda.set_device(dev)
-        call = (C.byref(plan.model), plan._pt_ref,
-                C.c_void_p(h_in.data_ptr()), C.c_void_p(ctl.data_ptr()),
-                C.c_void_p(h_out.data_ptr()), C.c_void_p(scratch.data_ptr()),
-                scratch.numel(), C.c_void_p(stream.cuda_stream), timeout)
-        pbar = util.trange(maxsteps, desc="BFGS Gradient Descent Progress",
-                           leave=True)
+    def callback(*_a, **_k):
+        if hasattr(pbar, "update"):
+            pbar.update()
 
-        def root_eval():
-            # ONE native call: control block H2D, NVLink push to the workers,
-            # gated fused launch, results polled in pinned host memory
-            rc = plan.lib.mgb_erfbin_bfgs_root_eval(*call)
-            if rc:
-                _lib.check(rc, "mgb_erfbin_bfgs_root_eval")
+    evaluate, end_session = model._host_session(x0)
+    nev = 0
 
-        def fn(p):
-            n_in[0] = 1.0
-            n_in[1:] = p
-            root_eval()
-            return float(n_out[0]), n_out[1:].astype(np.float64)
+    def fn(p):
+        nonlocal nev
+        if _before_eval is not None:
+            _before_eval(nev)
+        nev += 1
+        return evaluate(p)
 
-        def callback(*_a, **_k):
-            if hasattr(pbar, "update"):
-                pbar.update()
-
-        result, err = None, None
+    err = None
+    result = None
+    try:
+        result = scipy.optimize.minimize(
+            fn, x0=x0, method="L-BFGS-B", jac=True,
+            options=dict(maxiter=maxsteps), callback=callback,
+            bounds=param_bounds)
+    except BaseException as e:  # noqa: BLE001 - the waiting grid must go
+        err = e
+    finally:
         try:
-            result = scipy.optimize.minimize(
-                fn, x0=_np64(guess).ravel(), method="L-BFGS-B", jac=True,
-                options=dict(maxiter=maxsteps), callback=callback,
-                bounds=param_bounds)
-        except BaseException as e:  # noqa: BLE001 - workers must be released
-            err = e
-        finally:
-            if hasattr(pbar, "close"):
-                pbar.close()
-            n_in[:] = 0.0
-            for _ in range(DEPTH):
-                root_eval()             # gated no-op, keeps launch parity
-            stream.synchronize()
-        comm.bcast(("error", repr(err)) if err is not None else
-                   ("ok", [*result.keys()], [*result.values()]), root=0)
-        if err is not None:
-            raise err
-    else:
-        flags = torch.zeros(4 * DEPTH, dtype=torch.float32).pin_memory()
-        events = []
-        launched = 0
-
-        def enqueue():
-            nonlocal launched
-            slot = launched % (4 * DEPTH)
-            bcast_(ctl, comm, root=0)
-            plan.launch(a)
-            flags[slot:slot + 1].copy_(ctl[0:1], non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(stream)
-            events.append((ev, slot))
-            launched += 1
-
-        for _ in range(DEPTH):
-            enqueue()
-        exiting = False
-        while events:
-            ev, slot = events.pop(0)
-            ev.synchronize()
-            if not exiting and float(flags[slot]) != 0.0:
-                enqueue()
-            else:
-                exiting = True
-        msg = comm.bcast(None, root=0)
-        if msg[0] == "error":
-            raise RuntimeError(f"run_bfgs: the root rank raised {msg[1]}")
-        result = scipy.optimize.OptimizeResult(dict(zip(msg[1], msg[2])))
+            end_session()
+        except Exception as e2:  # noqa: BLE001
+            if err is None:
+                err = e2
+        if hasattr(pbar, "close"):
+            pbar.close()
+    # cold path: did every rank walk the same path?
+    mine = (repr(err) if err is not None else None, nev,
+            None if result is None else np.asarray(result.x).tobytes())
+    everyone = comm.allgather(mine)
+    if err is not None:
+        raise err
+    bad = [r for r, o in enumerate(everyone) if o[0] is not None]
+    if bad:
+        raise RuntimeError(f"run_bfgs: rank(s) {bad} raised "
+                           f"{everyone[bad[0]][0]}")
+    if any(o[1:] != everyone[0][1:] for o in everyone):
+        raise RuntimeError(
+            "run_bfgs: the ranks' optimisers diverged (evaluation counts "
+            f"{[o[1] for o in everyone]}): host L-BFGS-B is not deterministic "
+            "on this machine")
     model._check_peers()
     return result

@@ -265,7 +265,8 @@ class ErfBinnedModel(OnePointModel):
             out = self.plan().evaluate(p, MODE_SUMSTATS_JAC, reduce=total)
             return out["sumstats"], out["jac"]
         s, dmu, dsg = _ref.erf_binned_partial_and_jac(
-            self.x, self._edges_t, self._norm_t, p[self.mu_index],
+            self.x, self._edges_t.to(self.x.dtype), self._norm_t,
+            p[self.mu_index],
             p[self.sigma_index], self.sigma_link, self.weights)
         jac = torch.zeros(self.nbins, self.nparams, dtype=s.dtype,
                           device=s.device)
@@ -588,17 +589,20 @@ class ErfBinnedModel(OnePointModel):
 
     def run_bfgs(self, guess, maxsteps=100, param_bounds=None, randkey=None,
                  comm=None):
-        """L-BFGS-B on the host of rank 0 with one fused loss+gradient launch
-        per line-search evaluation.  With several GPUs the parameters are
-        handed to the workers by a device-side push (``mgb_bcast_f32``) and
-        the workers wait on the GPU: no host message per evaluation."""
+        """L-BFGS-B (scipy, float64, on the host) with one fused
+        loss+gradient launch per line-search evaluation, through an evaluation
+        session (a grid always pre-launched and waiting on the GPU).  With
+        several GPUs every rank runs the same deterministic optimiser on the
+        bit-identical reduced values (``models/bfgs_device.py``): no
+        parameter hand-off and no result broadcast."""
         if not (self.fused and self._builtin_loss):
             return super().run_bfgs(guess, maxsteps, param_bounds, randkey,
                                     comm)
         comm = self.comm if comm is None else comm
         if comm is not None and comm.size > 1:
-            from .bfgs_device import run_bfgs_device
-            return run_bfgs_device(self, guess, maxsteps, param_bounds, comm)
+            from .bfgs_device import run_bfgs_replicated
+            return run_bfgs_replicated(self, guess, maxsteps, param_bounds,
+                                       comm)
         if param_bounds is not None and hasattr(param_bounds, "tolist"):
             param_bounds = param_bounds.tolist()
         x0 = _np(guess).ravel()

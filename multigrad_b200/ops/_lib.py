@@ -231,10 +231,6 @@ def _declare(lib: C.CDLL) -> None:
         C.POINTER(MgbErfBinModel), C.POINTER(MgbPeerTable), vp, vp, vp, u64,
         vp, u32, i32, C.POINTER(u32)]
     lib.mgb_erfbin_host_session.restype = C.c_int
-    lib.mgb_erfbin_bfgs_root_eval.argtypes = [
-        C.POINTER(MgbErfBinModel), C.POINTER(MgbPeerTable), vp, vp, vp, vp,
-        u64, vp, u32]
-    lib.mgb_erfbin_bfgs_root_eval.restype = C.c_int
     lib.mgb_erfbin_step_static.argtypes = [C.POINTER(MgbErfBinModel),
                                            C.POINTER(MgbStepArgs),
                                            C.POINTER(MgbPeerTable), vp]

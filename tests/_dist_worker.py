@@ -177,6 +177,50 @@ def bfgs_all_ranks_same_result():
 
 
 @case
+def gpu_bfgs_rank_skew_stress():
+    """Host-driven evaluations (the body of the multi-GPU L-BFGS-B) with a
+    random delay injected on every rank in front of every evaluation: 1000
+    evaluations, every rank must read back the same bits each time, and a
+    complete run_bfgs under the same skew must still agree on all ranks
+    (stands in for the race detector that is closed on this
+    pool)."""
+    if DEV.type != "cuda" or SIZE < 2:
+        return
+    import random
+    import time as _time
+    from multigrad_b200.models.bfgs_device import run_bfgs_replicated
+    x = torch.log10(smf.load_halo_masses_tutorial(200_000, comm=COMM)).to(DEV)
+    edges = torch.linspace(9, 10, 11)
+    model = SMFModel(x=x, bin_edges=edges, volume=1.0, sigma_link="log10",
+                     loss_eps=1e-10, target_sumstats=torch.ones(10))
+    model.set_target(model.calc_sumstats_from_params([-2.0, -0.5]))
+    rnd = random.Random(1234 + RANK)
+    prm = random.Random(99)                      # same points on every rank
+    evaluate, end = model._host_session(np.array([-2.1, -0.4]))
+    digest = []
+    try:
+        for i in range(1000):
+            _time.sleep(rnd.random() * 3e-4 * (rnd.random() < 0.3))
+            p = np.array([-2.0 + 0.5 * (prm.random() - 0.5),
+                          -0.5 + 0.4 * (prm.random() - 0.5)])
+            loss, grad = evaluate(p)
+            digest.append(np.float64(loss).tobytes() + grad.tobytes())
+    finally:
+        end()
+    blobs = COMM.allgather(b"".join(digest))
+    assert all(b == blobs[0] for b in blobs)
+    COMM.workspace().check_error()
+
+    def skew(_n):
+        _time.sleep(rnd.random() * 5e-4 * (rnd.random() < 0.5))
+    res = run_bfgs_replicated(model, np.array([-3.5, 0.2]), 100, None, COMM,
+                              _before_eval=skew)
+    assert res.success and np.allclose(res.x, [-2.0, -0.5], atol=2e-4), res
+    xs = COMM.allgather((np.asarray(res.x).tobytes(), int(res.nfev)))
+    assert all(v == xs[0] for v in xs)
+
+
+@case
 def group_of_models():
     """OnePointGroup over disjoint sub-communicators == sum of the models
     evaluated on all the data (config W4: multi-redshift SMF)."""

@@ -15,7 +15,8 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 WORKER = Path(__file__).with_name("_dist_worker.py")
 CASES = CPU_CASES + ["gpu_allreduce_kernels", "gpu_fused_step_uses_one_launch",
                      "gpu_linear_link_world_invariance",
-                     "gpu_scatter_nd_over_nvlink", "gpu_group_device_steps"]
+                     "gpu_scatter_nd_over_nvlink", "gpu_group_device_steps",
+                     "gpu_bfgs_rank_skew_stress"]
 
 
 def _worlds():
