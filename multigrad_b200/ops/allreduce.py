@@ -69,9 +69,13 @@ def all_reduce_sum_(t: torch.Tensor, comm, algo: int = 0) -> torch.Tensor:
             return t
         # large float32 messages: reduce inside the NVLink switch when the
         # communicator has a multicast buffer (collective lazy set-up)
+        # A tensor from PeerWorkspace.multicast_tensor() (same offset on every
+        # rank, checked when it was allocated) is reduced in place; every rank
+        # has to pass the same kind of tensor to a collective call.
         resident = (dt == 0 and ws._mc and (algo == 4 or (
                     algo == 0 and comm.size >= NVLS_MIN_WORLD)) and
-                    ws._mc.uc <= t.data_ptr() < ws._mc.uc + ws._mc.bytes and
+                    ws._mc.uc <= t.data_ptr() and
+                    t.data_ptr() + n * 4 <= ws._mc.uc + ws._mc.alloc_bytes and
                     n * 4 >= NVLS_INPLACE_MIN_BYTES)
         if resident or (dt == 0 and (algo == 4 or (
                 algo == 0 and n * 4 >= NVLS_MIN_BYTES
@@ -82,13 +86,22 @@ def all_reduce_sum_(t: torch.Tensor, comm, algo: int = 0) -> torch.Tensor:
                                    "available on this communicator")
             if mc is not None:
                 flat = t.view(-1)
-                # a tensor that lives in the bound buffer is reduced in place
-                # by the kernel (no staging), otherwise staged in chunks
-                step = n if resident else mc.bytes // 4
+                if resident:
+                    # reduced in place by the kernel, no staging
+                    _lib.check(lib.mgb_allreduce_sum_nvls(
+                        C.byref(ws.table), mc.uc, mc.mc, mc.bytes,
+                        flat.data_ptr(), n, _stream()),
+                        "mgb_allreduce_sum_nvls")
+                    _LAUNCHES += 1
+                    return t
+                # staged in chunks through the upper half of the bound buffer
+                # (the lower half belongs to the symmetric tensors)
+                step = mc.stage_bytes // 4
                 for lo in range(0, n, step):
                     c = flat[lo:lo + step]
                     _lib.check(lib.mgb_allreduce_sum_nvls(
-                        C.byref(ws.table), mc.uc, mc.mc, mc.bytes,
+                        C.byref(ws.table), mc.uc + mc.stage_off,
+                        mc.mc + mc.stage_off, mc.stage_bytes,
                         c.data_ptr(), c.numel(), _stream()),
                         "mgb_allreduce_sum_nvls")
                     _LAUNCHES += 1

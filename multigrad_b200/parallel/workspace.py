@@ -30,12 +30,20 @@ DEFAULT_TIMEOUT_MS = 20000
 
 
 class _Multicast:
-    """Handles and the two views of a multicast-bound buffer."""
-    __slots__ = ("handle", "mem", "uc", "mc", "bytes")
+    """Handles and the two views of a multicast-bound buffer.  The buffer is
+    split in two: ``[0, alloc_bytes)`` holds the symmetric tensors handed out
+    by ``PeerWorkspace.multicast_tensor``, ``[stage_off, bytes)`` is the
+    staging window through which ordinary tensors are reduced -- the two never
+    overlap, so a staged reduction cannot overwrite a resident tensor."""
+    __slots__ = ("handle", "mem", "uc", "mc", "bytes", "alloc_bytes",
+                 "stage_off", "stage_bytes")
 
     def __init__(self, handle, mem, uc, mc, nbytes):
         self.handle, self.mem = handle, mem
         self.uc, self.mc, self.bytes = uc, mc, nbytes
+        self.alloc_bytes = (nbytes // 2) & ~4095
+        self.stage_off = self.alloc_bytes
+        self.stage_bytes = nbytes - self.stage_off
 
 
 class PeerWorkspace:
@@ -104,7 +112,8 @@ class PeerWorkspace:
     def multicast_tensor(self, numel: int, dtype=torch.float32):
         """A zeroed CUDA tensor carved out of the multicast-bound buffer
         (symmetric memory: every rank must make the same sequence of calls so
-        that the tensors sit at the same offsets).  ``reduce_sum`` /
+        that the tensors sit at the same offsets -- checked here, this is a
+        collective call).  ``reduce_sum`` /
         ``all_reduce_sum_`` on such a tensor runs entirely inside the NVLink
         switch, without staging copies.  ``None`` when multicast is
         unavailable or the buffer is exhausted."""
@@ -113,9 +122,21 @@ class PeerWorkspace:
             return None
         esz = torch.empty(0, dtype=dtype).element_size()
         nbytes = (numel * esz + 255) & ~255
-        if self._mc_used + nbytes > mc.bytes:
+        # the upper half of the bound buffer is the staging window of the
+        # reductions of ordinary tensors (ops/allreduce.py): symmetric
+        # tensors only ever live in the lower half
+        if self._mc_used + nbytes > mc.alloc_bytes:
             return None
-        ptr = mc.uc + self._mc_used
+        offset = self._mc_used
+        # every rank must be at the same offset, or the in-switch reduction
+        # would add unrelated memory (and ranks would pick different kernels)
+        offs = self.comm.allgather((offset, nbytes))
+        if any(o != offs[0] for o in offs):
+            raise RuntimeError(
+                "multicast_tensor: ranks are at different offsets of the "
+                f"symmetric buffer ({offs}); every rank has to make the same "
+                "sequence of multicast_tensor() calls")
+        ptr = mc.uc + offset
         self._mc_used += nbytes
         typestr = {torch.float32: "<f4", torch.float64: "<f8",
                    torch.int32: "<i4", torch.uint8: "|u1"}[dtype]

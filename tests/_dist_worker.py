@@ -361,6 +361,21 @@ def gpu_allreduce_kernels():
             err = (a.double().cpu() - want).abs().max() / want.abs().max()
             assert err < 1e-6 * SIZE, ("nvls inplace", rep, float(err))
             assert bool((b == 7.0).all())
+        # a staged (non-resident) reduction of a large ordinary tensor must
+        # not touch the symmetric tensors: it stages through its own window
+        keep_a = a.clone()
+        big = torch.randn(SIZE, (5 << 20) // 4 + 3, generator=g)
+        for rep in range(2):
+            out = ar.all_reduce_sum(big[RANK].to(DEV), COMM, algo=4)
+            want = big.double().sum(0)
+            err = (out.double().cpu() - want).abs().max() / want.abs().max()
+            assert err < 1e-6 * SIZE, ("nvls staged", rep, float(err))
+            assert torch.equal(a, keep_a) and bool((b == 7.0).all())
+        # back-to-back broadcasts from alternating roots (ack protocol)
+        for rep in range(50):
+            v = torch.full((9,), float(rep + RANK), device=DEV)
+            ar.bcast_(v, COMM, root=rep % SIZE)
+            assert torch.all(v == rep + rep % SIZE)
         print(f"[rank {RANK}] NVLS all-reduce checked", flush=True)
     # integer tensors go through float64
     t = mg.reduce_sum(torch.arange(5, device=DEV) * (RANK + 1))
