@@ -209,6 +209,10 @@ typedef struct MgbStepArgs {
   /* Optional device buffer of %globaltimer stamps (tools/step_trace.py):
    * per step 8 + 2*grid uint64 words; NULL = no tracing. */
   uint64_t* trace;
+  /* step index mixed into the device-side random key of a stochastic link
+   * (evaluation modes; the optimiser modes use *opt_step) */
+  uint32_t rng_step;
+  uint32_t reserved1;
 } MgbStepArgs;
 
 /* scratch needed by mgb_erfbin_step: bytes for `scratch` given the batch */
@@ -280,6 +284,37 @@ int mgb_erfbin_adam_host(const MgbErfBinModel* model, const MgbPeerTable* pt,
 int mgb_erfbin_step_static(const MgbErfBinModel* model,
                            const MgbStepArgs* args, const MgbPeerTable* pt,
                            void* stream);
+
+/* ------------------------------------------------------------------------
+ * K1/K2/K3 for user-defined links (csrc/linkbin.cu, compiled per model from a
+ * header generated by multigrad_b200/link.py): mu_h = x_h + shift(x_h, f_h;
+ * p), sigma_h = sigma(x_h, f_h; p) with up to MGB_LINK_MAX_FEAT per-object
+ * feature columns.  Replaces jax.vjp of an arbitrary user sumstats function
+ * (OnePointModel._vjp, multigrad/multigrad.py:508-538) for the soft-binned
+ * family; the per-step random key (multigrad/adam.py:60-62) is derived on the
+ * device from (seed, step).  Entry points live in the per-model library:
+ * mgb_linkbin_step / mgb_linkbin_scratch_bytes / mgb_linkbin_nparams / ...
+ * ---------------------------------------------------------------------- */
+#define MGB_LINK_MAX_FEAT 4
+typedef struct MgbLinkModel {
+  const float* x;        /* object coordinate [n]                            */
+  const float* w;        /* optional per-object weight [n] or NULL           */
+  const float* feat[MGB_LINK_MAX_FEAT]; /* feature columns [n] each          */
+  int64_t n;
+  int64_t index0;        /* global index of this shard's first object (RNG)  */
+  uint64_t seed;         /* random seed of a stochastic link                 */
+  int32_t nbins, nparams, nfeat, loss_kind;
+  float loss_eps, x0;
+  double edges[MGB_MAX_BINS + 1];
+  float norm[MGB_MAX_BINS];
+  float target[MGB_MAX_BINS];
+  float inv_err[MGB_MAX_BINS];
+} MgbLinkModel;
+uint64_t mgb_linkbin_scratch_bytes(int nbins);
+/* `scratch` must be zero-filled once before its first use. */
+int mgb_linkbin_step(const MgbLinkModel* model, const MgbStepArgs* args,
+                     const MgbPeerTable* pt, void* scratch,
+                     uint64_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
  * Linear-link soft-binned statistic on the tensor cores (tcgen05 + TMEM +

@@ -87,6 +87,7 @@ class MgbStepArgs(C.Structure):
         ("wait_timeout_ms", C.c_uint32),
         ("nsteps", C.c_int32), ("flags", C.c_int32),
         ("trace", C.c_void_p),
+        ("rng_step", C.c_uint32), ("reserved1", C.c_uint32),
     ]
 
 
