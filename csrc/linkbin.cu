@@ -373,7 +373,9 @@ linkbin_step_kernel(const __grid_constant__ MgbLinkModel md,
   __syncthreads();
   // per-step key of the stochastic links: the same on every rank
   const unsigned step =
-      (a.mode >= MGB_MODE_ADAM) ? (unsigned)__ldcg(a.opt_step) : a.rng_step;
+      (a.mode >= MGB_MODE_ADAM && !(a.flags & MGB_STEP_CONST_KEY))
+          ? (unsigned)__ldcg(a.opt_step)
+          : a.rng_step;
   const unsigned long long key =
       ul_mix(md.seed ^ ul_mix(0x5851F42D4C957F2Dull + step));
 

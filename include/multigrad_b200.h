@@ -162,6 +162,10 @@ enum {
  * selected for every launch by the environment variable
  * MULTIGRAD_B200_DETERMINISTIC=1). */
 #define MGB_STEP_STATIC_SPLIT 1
+/* CONST_KEY (stochastic links, csrc/linkbin.cu): the optimiser modes use
+ * rng_step instead of the running step index for the random key, i.e. the
+ * same draws at every step (const_randkey of multigrad/multigrad.py:291-297). */
+#define MGB_STEP_CONST_KEY 2
 
 typedef struct MgbStepArgs {
   int32_t mode;

@@ -105,6 +105,7 @@ class MgbGroupArgs(C.Structure):
 
 MODE_SUMSTATS, MODE_SUMSTATS_JAC, MODE_LOSS_GRAD, MODE_ADAM, MODE_GD = range(5)
 STEP_STATIC_SPLIT = 1
+STEP_CONST_KEY = 2
 
 
 def nvcc_path() -> Optional[str]:
