@@ -123,8 +123,19 @@ static_assert(UL_NP >= 1 && UL_NP <= MGB_MAX_PARAMS, "UL_NP out of range");
 #define UL_HSCALE (MGB_ERFCX_CSCALE / UL_KAPPA)
 #define UL_ZS_SKIP 12.4f
 #define UL_SENTINEL_X 1.0e30f
-#define UL_ET 4                      // edges per warp
+// Edges per warp (every warp of a group re-evaluates the link for its
+// objects, so fewer, wider groups are better) limited by the accumulator
+// registers, (2 + P) per edge: one group of up to 11 edges for P <= 3.
+#if UL_NP <= 3
+#define UL_ET 11
+#elif UL_NP <= 5
+#define UL_ET 6
+#else
+#define UL_ET 4
+#endif
+#define UL_CHUNK 3                   // edges per software-pipeline stage
 #define UL_MAX_WARPS 12
+#define UL_WIDE (UL_ET > 4)          // wide: one CTA of 12 warps per SM
 #define UL_MAX_EDGES (MGB_MAX_BINS + 1)
 #define UL_MAX_GROUPS ((UL_MAX_EDGES + UL_ET - 1) / UL_ET)
 #define UL_NQ (2 + UL_NP)            // T, O, J_0 .. J_{P-1} per edge
@@ -141,74 +152,111 @@ struct UlAcc {
   float J[UL_NP];
 };
 
-// one pair of objects against the ET edges of a group
-template <int ET, bool WEIGHTED>
+// Stage A of a chunk of edges [e0, e0+CH): scaled coordinate, t = 1/(1+h|zs|)
+// and Gaussian of every edge -- the MUFU work.
+template <int ET, int CH>
+__device__ __forceinline__ void ul_stage_a(const float* __restrict__ ec,
+                                           float2 inv, float2 b, float2 wt,
+                                           int e0, float2* zs, float2* g,
+                                           float2* t) {
+#pragma unroll
+  for (int j = 0; j < CH; ++j)
+    if (e0 + j < ET) zs[j] = vfma(f2s(ec[e0 + j]), inv, b);
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (e0 + j < ET) {
+      const float2 d = vfma(f2(fabsf(zs[j].x), fabsf(zs[j].y)),
+                            f2s(UL_HSCALE), f2s(1.0f));
+      t[j] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (e0 + j < ET) {
+      const float2 zz = vmul(zs[j], zs[j]);
+      g[j] = vmul(f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y)), wt);
+    }
+  }
+}
+
+// Stage B: Horner polynomial and the accumulations -- the FMA work.
+//   T += -+ 1/2 erfc|z| w,  O += [z >= 0] w,  J_k += g U_k + (zs g) V_k
+template <int ET, int CH>
+__device__ __forceinline__ void ul_stage_b(UlAcc* __restrict__ a, int e0,
+                                           const float2* zs, const float2* g,
+                                           const float2* t, float2 wt,
+                                           const float2* U, const float2* V) {
+  float2 p[CH];
+  constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
+#pragma unroll
+  for (int j = 0; j < CH; ++j)
+    if (e0 + j < ET)
+      p[j] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[j],
+                  f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
+#pragma unroll
+  for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+      if (e0 + j < ET) p[j] = vfma(p[j], t[j], f2s(0.5f * kC[d]));
+  }
+#pragma unroll
+  for (int j = 0; j < CH; ++j)
+    if (e0 + j < ET) p[j] = vmul(p[j], t[j]);
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (e0 + j < ET) {
+      UlAcc& ac = a[e0 + j];
+      const float gx = __uint_as_float(
+          __float_as_uint(g[j].x) | (~__float_as_uint(zs[j].x) & 0x80000000u));
+      const float gy = __uint_as_float(
+          __float_as_uint(g[j].y) | (~__float_as_uint(zs[j].y) & 0x80000000u));
+      ac.T = fmaf(p[j].x, gx, ac.T);
+      ac.T = fmaf(p[j].y, gy, ac.T);
+      ac.O += zs[j].x >= 0.0f ? wt.x : 0.0f;
+      ac.O += zs[j].y >= 0.0f ? wt.y : 0.0f;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < CH; ++j) {
+    if (e0 + j < ET) {
+      UlAcc& ac = a[e0 + j];
+      const float2 zg = vmul(zs[j], g[j]);
+#pragma unroll
+      for (int k = 0; k < UL_NP; ++k) {
+        if ((UL_MU_MASK >> k) & 1) {
+          ac.J[k] = fmaf(g[j].x, U[k].x, ac.J[k]);
+          ac.J[k] = fmaf(g[j].y, U[k].y, ac.J[k]);
+        }
+        if ((UL_SG_MASK >> k) & 1) {
+          ac.J[k] = fmaf(zg.x, V[k].x, ac.J[k]);
+          ac.J[k] = fmaf(zg.y, V[k].y, ac.J[k]);
+        }
+      }
+    }
+  }
+}
+
+// one pair of objects against the ET edges of a group; the MUFU stage of the
+// next chunk is issued ahead of the FMA stage of the current one (see
+// csrc/erfbin.cu: with three warps per scheduler a warp has to keep both
+// pipes busy by itself)
+template <int ET>
 __device__ __forceinline__ void ul_pair(UlAcc* __restrict__ a,
                                         const float* __restrict__ ec,
                                         float2 muc, float2 inv, float2 wt,
                                         const float2* U, const float2* V) {
+  constexpr int CH = UL_CHUNK < ET ? UL_CHUNK : ET;
+  constexpr int NCH = (ET + CH - 1) / CH;
   // zs_e = (ec_e - muc) inv = ec_e inv + b
   const float2 b = vneg(vmul(muc, inv));
-  float2 zs[ET], t[ET], g[ET], p[ET];
+  float2 zs[2][CH], g[2][CH], t[2][CH];
+  ul_stage_a<ET, CH>(ec, inv, b, wt, 0, zs[0], g[0], t[0]);
 #pragma unroll
-  for (int e = 0; e < ET; ++e) zs[e] = vfma(f2s(ec[e]), inv, b);
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 d = vfma(f2(fabsf(zs[e].x), fabsf(zs[e].y)), f2s(UL_HSCALE),
-                          f2s(1.0f));
-    t[e] = f2(mgb_rcp(d.x), mgb_rcp(d.y));
-  }
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 zz = vmul(zs[e], zs[e]);
-    g[e] = f2(mgb_ex2(-zz.x), mgb_ex2(-zz.y));
-    if (WEIGHTED) g[e] = vmul(g[e], wt);
-  }
-  constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
-#pragma unroll
-  for (int e = 0; e < ET; ++e)
-    p[e] = vfma(f2s(0.5f * kC[MGB_ERFCX_DEG]), t[e],
-                f2s(0.5f * kC[MGB_ERFCX_DEG - 1]));
-#pragma unroll
-  for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
-#pragma unroll
-    for (int e = 0; e < ET; ++e) p[e] = vfma(p[e], t[e], f2s(0.5f * kC[d]));
-  }
-#pragma unroll
-  for (int e = 0; e < ET; ++e) p[e] = vmul(p[e], t[e]);
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float gx = __uint_as_float(
-        __float_as_uint(g[e].x) | (~__float_as_uint(zs[e].x) & 0x80000000u));
-    const float gy = __uint_as_float(
-        __float_as_uint(g[e].y) | (~__float_as_uint(zs[e].y) & 0x80000000u));
-    a[e].T = fmaf(p[e].x, gx, a[e].T);
-    a[e].T = fmaf(p[e].y, gy, a[e].T);
-    if (WEIGHTED) {
-      a[e].O += zs[e].x >= 0.0f ? wt.x : 0.0f;
-      a[e].O += zs[e].y >= 0.0f ? wt.y : 0.0f;
-    } else {
-      int cnt = __float_as_int(a[e].O);
-      cnt += (int)(__float_as_uint(zs[e].x) >> 31);
-      cnt += (int)(__float_as_uint(zs[e].y) >> 31);
-      a[e].O = __int_as_float(cnt);
-    }
-  }
-  // Jacobian: J_k += g U_k + (zs g) V_k, only the terms that exist
-#pragma unroll
-  for (int e = 0; e < ET; ++e) {
-    const float2 zg = vmul(zs[e], g[e]);
-#pragma unroll
-    for (int k = 0; k < UL_NP; ++k) {
-      if ((UL_MU_MASK >> k) & 1) {
-        a[e].J[k] = fmaf(g[e].x, U[k].x, a[e].J[k]);
-        a[e].J[k] = fmaf(g[e].y, U[k].y, a[e].J[k]);
-      }
-      if ((UL_SG_MASK >> k) & 1) {
-        a[e].J[k] = fmaf(zg.x, V[k].x, a[e].J[k]);
-        a[e].J[k] = fmaf(zg.y, V[k].y, a[e].J[k]);
-      }
-    }
+  for (int n = 0; n < NCH; ++n) {
+    if (n + 1 < NCH)
+      ul_stage_a<ET, CH>(ec, inv, b, wt, (n + 1) * CH, zs[(n + 1) & 1],
+                         g[(n + 1) & 1], t[(n + 1) & 1]);
+    ul_stage_b<ET, CH>(a, n * CH, zs[n & 1], g[n & 1], t[n & 1], wt, U, V);
   }
 }
 
@@ -244,19 +292,22 @@ __device__ __forceinline__ void ul_fetch(const MgbLinkModel& md, long long i,
     t.w = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int j = 0; j < UL_NF; ++j) t.f[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i == n4) {  // ragged tail
+    if (i == n4) {  // ragged tail: the last n % 4 objects
       const long long b4 = n4 << 2;
       const int rem = (int)(md.n - b4);
-      float* xs = &t.x.x;
-      float* ws = &t.w.x;
-      for (int r = 0; r < rem; ++r) {
-        xs[r] = md.x[b4 + r];
-        if (WEIGHTED) ws[r] = md.w[b4 + r];
+      if (rem > 0) t.x.x = md.x[b4];
+      if (rem > 1) t.x.y = md.x[b4 + 1];
+      if (rem > 2) t.x.z = md.x[b4 + 2];
+      if (WEIGHTED) {
+        if (rem > 0) t.w.x = md.w[b4];
+        if (rem > 1) t.w.y = md.w[b4 + 1];
+        if (rem > 2) t.w.z = md.w[b4 + 2];
       }
 #pragma unroll
       for (int j = 0; j < UL_NF; ++j) {
-        float* fs = &t.f[j].x;
-        for (int r = 0; r < rem; ++r) fs[r] = md.feat[j][b4 + r];
+        if (rem > 0) t.f[j].x = md.feat[j][b4];
+        if (rem > 1) t.f[j].y = md.feat[j][b4 + 1];
+        if (rem > 2) t.f[j].z = md.feat[j][b4 + 2];
       }
     }
   }
@@ -329,9 +380,8 @@ __device__ __forceinline__ void ul_accumulate(
                           f2s(-0.5641895835477563f / UL_KAPPA))
                    : f2s(0.f);
       }
-      // every object is weighted here (weight 1 or 0 without user weights):
-      // the kernels are instantiated WEIGHTED only
-      ul_pair<ET, true>(acc, ec, muc, inv, wt, U, V);
+      // every object carries a weight here (1 or 0 without user weights)
+      ul_pair<ET>(acc, ec, muc, inv, wt, U, V);
     }
   }
 #pragma unroll
@@ -350,8 +400,28 @@ __device__ __forceinline__ void ul_accumulate(
   }
 }
 
+// models with few edges: groups narrower than UL_ET - 1
 template <bool WEIGHTED>
-__global__ void __launch_bounds__(UL_MAX_WARPS * 32, 2)
+__device__ __noinline__ void ul_accumulate_small(
+    const MgbLinkModel& md, const float* __restrict__ ec_all, int e_first,
+    int et, const float* __restrict__ pv, unsigned long long key, int wj,
+    int wpg, int lane, double* s_out) {
+  switch (et) {
+#define UL_CASE(n)                                                          \
+  case n:                                                                   \
+    if (n < UL_ET - 1)                                                      \
+      ul_accumulate<(n < UL_ET - 1 ? n : 1), WEIGHTED>(                     \
+          md, ec_all, e_first, pv, key, wj, wpg, lane, s_out);              \
+    break;
+    UL_CASE(1) UL_CASE(2) UL_CASE(3) UL_CASE(4) UL_CASE(5) UL_CASE(6)
+    UL_CASE(7) UL_CASE(8) UL_CASE(9)
+#undef UL_CASE
+    default: break;
+  }
+}
+
+template <bool WEIGHTED>
+__global__ void __launch_bounds__(UL_MAX_WARPS * 32, UL_WIDE ? 1 : 2)
 linkbin_step_kernel(const __grid_constant__ MgbLinkModel md,
                     const __grid_constant__ MgbStepArgs a,
                     const __grid_constant__ MgbPeerTable pt,
@@ -386,16 +456,17 @@ linkbin_step_kernel(const __grid_constant__ MgbLinkModel md,
     const int et = lay.e0[g + 1] - e_first;
     const int wpg = lay.w0[g + 1] - lay.w0[g];
     const int wj = warp - lay.w0[g];
-    switch (et) {
-      case 4: ul_accumulate<4, WEIGHTED>(md, sh.ec, e_first, sh.pv, key, wj,
-                                         wpg, lane, sh.warp[warp]); break;
-      case 3: ul_accumulate<3, WEIGHTED>(md, sh.ec, e_first, sh.pv, key, wj,
-                                         wpg, lane, sh.warp[warp]); break;
-      case 2: ul_accumulate<2, WEIGHTED>(md, sh.ec, e_first, sh.pv, key, wj,
-                                         wpg, lane, sh.warp[warp]); break;
-      default: ul_accumulate<1, WEIGHTED>(md, sh.ec, e_first, sh.pv, key, wj,
-                                          wpg, lane, sh.warp[warp]); break;
-    }
+    // groups hold UL_ET or UL_ET - 1 edges (make_layout), fewer only when the
+    // model has fewer edges than that
+    if (et == UL_ET)
+      ul_accumulate<UL_ET, WEIGHTED>(md, sh.ec, e_first, sh.pv, key, wj, wpg,
+                                     lane, sh.warp[warp]);
+    else if (et == UL_ET - 1 && UL_ET > 1)
+      ul_accumulate<(UL_ET > 1 ? UL_ET - 1 : 1), WEIGHTED>(
+          md, sh.ec, e_first, sh.pv, key, wj, wpg, lane, sh.warp[warp]);
+    else
+      ul_accumulate_small<WEIGHTED>(md, sh.ec, e_first, et, sh.pv, key, wj,
+                                    wpg, lane, sh.warp[warp]);
   }
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   __syncthreads();
@@ -507,7 +578,7 @@ UlLayout ul_make_layout(int nbins) {
     L.e0[g] = e;
     L.w0[g] = w;
     e += et;
-    w += (L.ng == 1) ? 8 : ((E <= UL_MAX_WARPS) ? et : even);
+    w += (L.ng == 1) ? UL_MAX_WARPS : ((E <= UL_MAX_WARPS) ? et : even);
   }
   L.e0[L.ng] = e;
   L.w0[L.ng] = w;
@@ -521,7 +592,7 @@ int ul_grid(int nbins) {
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) !=
       cudaSuccess)
     return 0;
-  return sms * 2;
+  return sms * (UL_WIDE ? 1 : 2);
 }
 
 }  // namespace
