@@ -221,6 +221,117 @@ def gpu_bfgs_rank_skew_stress():
 
 
 @case
+def gpu_collective_soak():
+    """Stand-in for the race detector that is closed on this pool (SURVEY.md
+    5.2): MGB_SOAK_ITERS (default 2000; the committed 8-GPU log uses 10000)
+    collectives of every kind in a pseudo-random order that all ranks share --
+    ordered LL, one-shot push, two-shot, NVLS (staged and in place),
+    broadcast, fused evaluation, fused persistent steps -- each behind a
+    random per-rank delay on the host AND on the device (a spinning kernel in
+    front of the collective), every result compared on the device with the
+    exact expected sum; no mismatch and no sticky timeout flag allowed."""
+    if DEV.type != "cuda" or SIZE < 2:
+        return
+    import os
+    import random
+    import time as _time
+    from multigrad_b200.ops import allreduce as ar
+    iters = int(os.environ.get("MGB_SOAK_ITERS", "2000"))
+    shared = random.Random(4242)            # same choices on every rank
+    mine = random.Random(777 + RANK)        # this rank's delays
+    ws = COMM.workspace()
+    have_mc = ws.multicast() is not None
+    sym = ws.multicast_tensor(1 << 18) if have_mc else None
+    sizes = {1: [1, 7, 240], 3: [1000, 65_536], 2: [50_000, 300_000],
+             4: [4096, 1 << 19]}
+    bad = torch.zeros(1, dtype=torch.int64, device=DEV)
+    tri = SIZE * (SIZE + 1) // 2
+    data = _data(20_000)
+    model = SMFModel(aux_data=data, deterministic=True)   # bit-repeatable
+    ref_loss, ref_grad = model.calc_loss_and_grad_from_params([-1.9, 0.3])
+    ref_traj = model.run_adam([-1.9, 0.3], nsteps=3)
+    kinds = ["ll", "push", "two", "bcast", "eval", "fit"] + \
+        (["nvls", "nvls_inplace"] if have_mc else [])
+    for i in range(iters):
+        kind = shared.choice(kinds)
+        mult = float(shared.randrange(1, 8))
+        if mine.random() < 0.2:
+            _time.sleep(mine.random() * 2e-4)
+        if mine.random() < 0.5:
+            torch.cuda._sleep(int(mine.random() * 200_000))    # device skew
+        if kind in ("ll", "push", "two", "nvls"):
+            algo = {"ll": 1, "push": 3, "two": 2, "nvls": 4}[kind]
+            n = shared.choice(sizes[algo])
+            t = torch.full((n,), mult * (RANK + 1), device=DEV)
+            ar.all_reduce_sum_(t, COMM, algo=algo)
+            bad += (t != mult * tri).any()
+        elif kind == "nvls_inplace":
+            sym.fill_(mult * (RANK + 1))
+            ar.all_reduce_sum_(sym, COMM)
+            bad += (sym != mult * tri).any()
+        elif kind == "bcast":
+            root = shared.randrange(SIZE)
+            t = torch.full((9,), mult * (RANK + 1), device=DEV)
+            ar.bcast_(t, COMM, root=root)
+            bad += (t != mult * (root + 1)).any()
+        elif kind == "eval":
+            l, g = model.calc_loss_and_grad_from_params([-1.9, 0.3])
+            bad += (l != ref_loss) | (g != ref_grad).any()
+        else:
+            tr = model.run_adam([-1.9, 0.3], nsteps=3)
+            bad += (tr != ref_traj).any()
+        if i % 500 == 499:
+            torch.cuda.synchronize()
+            ws.check_error()
+    torch.cuda.synchronize()
+    ws.check_error()
+    nbad = COMM.allgather(int(bad.item()))
+    assert sum(nbad) == 0, nbad
+    print(f"[rank {RANK}] soak: {iters} mixed collectives, 0 mismatches",
+          flush=True)
+
+
+@case
+def gpu_linked_model_world_invariance():
+    """User-defined link on several GPUs: reduced statistic, Jacobian and a
+    fused Adam fit are those of the whole catalogue on one GPU, stochastic
+    draws follow the global object index."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.models import LinkedBinnedModel
+    n = 30_011
+    g = torch.Generator().manual_seed(21)
+    x_all = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    f_all = torch.randn(n, generator=g).float()
+    edges = np.linspace(9, 10, 11)
+
+    def lk(x, feat, p, rng):
+        return (x + p[0] + 0.05 * feat[0] + p[3] * rng.normal(0),
+                p[1] + p[2] * (x - 11.0))
+    lo, hi = (n * RANK) // SIZE, (n * (RANK + 1)) // SIZE
+    kw = dict(link=lk, nparams=4, bin_edges=edges, volume=10.0 * n, seed=5)
+    part = LinkedBinnedModel(x=x_all[lo:hi].to(DEV),
+                             features=[f_all[lo:hi].to(DEV)], **kw)
+    assert part.index0 == lo
+    whole = LinkedBinnedModel(x=x_all.to(DEV), features=[f_all.to(DEV)],
+                              comm=mg.Comm(None), **kw)
+    p = [-1.8, 0.3, 0.04, 0.1]
+    s1, j1 = part.calc_sumstats_and_jac_from_params(p, step=2)
+    s0, j0 = whole.calc_sumstats_and_jac_from_params(p, step=2)
+    assert torch.allclose(s1, s0, rtol=2e-6)
+    assert torch.allclose(j1, j0, rtol=2e-5, atol=2e-6 * float(j0.abs().max()))
+    tgt = whole.calc_sumstats_from_params([-2.0, 0.25, 0.02, 0.1])
+    part.set_target(tgt)
+    whole.set_target(tgt)
+    t1 = part.run_adam(p, nsteps=25, randkey=9)
+    t0 = whole.run_adam(p, nsteps=25, randkey=9)
+    assert torch.allclose(t1, t0, atol=2e-5)
+    blobs = COMM.allgather(t1.cpu().numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
+    COMM.workspace().check_error() if SIZE > 1 else None
+
+
+@case
 def group_of_models():
     """OnePointGroup over disjoint sub-communicators == sum of the models
     evaluated on all the data (config W4: multi-redshift SMF)."""
@@ -274,6 +385,20 @@ def experimental_scan_gd():
         {"x": mine.to(DEV)}, loss_and_grad, torch.zeros(1, device=DEV),
         learning_rate=1e-3, nsteps=50)
     assert len(df) == 50 and abs(df["params"].iloc[-1][0] - 2.0) < 0.05
+    if DEV.type == "cuda":
+        # the captured-graph loop (collective inside the graph) and the eager
+        # loop walk the same path, without a collective launch from Python
+        from multigrad_b200.ops import allreduce as ar
+        n0 = ar.launch_count()
+        dfe = scan_gd.simple_grad_descent(
+            {"x": mine.to(DEV)}, loss_and_grad, torch.zeros(1, device=DEV),
+            learning_rate=1e-3, nsteps=50, use_graph=False)
+        n_eager = ar.launch_count() - n0
+        assert np.allclose(np.stack(df["params"]), np.stack(dfe["params"]),
+                           rtol=1e-5, atol=1e-6)
+        assert np.allclose(df["loss"], dfe["loss"], rtol=1e-5)
+        if SIZE > 1:
+            assert n_eager == 50
 
 
 @case

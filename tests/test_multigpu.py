@@ -16,7 +16,8 @@ WORKER = Path(__file__).with_name("_dist_worker.py")
 CASES = CPU_CASES + ["gpu_allreduce_kernels", "gpu_fused_step_uses_one_launch",
                      "gpu_linear_link_world_invariance",
                      "gpu_scatter_nd_over_nvlink", "gpu_group_device_steps",
-                     "gpu_bfgs_rank_skew_stress"]
+                     "gpu_bfgs_rank_skew_stress", "gpu_collective_soak",
+                     "gpu_linked_model_world_invariance"]
 
 
 def _worlds():
