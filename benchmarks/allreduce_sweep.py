@@ -18,6 +18,7 @@ import sys
 from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+os.environ.setdefault("MULTIGRAD_B200_NO_TQDM", "1")
 import torch
 import torch.distributed as dist
 import multigrad_b200 as mg
@@ -41,6 +42,10 @@ def main():
         sizes.append(n)
         n *= 4
     sizes = [2, 8, 30] + [s for s in sizes if s > 30]
+    top = int(args.max_mb * (1 << 20)) // 4
+    if top not in sizes and top > sizes[-1]:
+        sizes.append(top)              # the 64 MiB end point of W5
+    from bench import ClockSampler
 
     def timed(fn, iters):
         for _ in range(5):
@@ -65,6 +70,9 @@ def main():
     for n in sizes:
         x = torch.randn(n, device=dev)
         iters = args.iters if n < (1 << 22) else max(10, args.iters // 5)
+        clk = ClockSampler(world) if rank == 0 else None
+        if clk:
+            clk.start()
         ours = timed(lambda: ar.all_reduce_sum_(x, comm), iters)
         nccl = timed(lambda: dist.all_reduce(x, group=comm.group), iters)
         forced = {}
@@ -94,6 +102,11 @@ def main():
                "nccl_us": round(nccl, 2), "ours_busbw_gbs": round(bus(ours), 2),
                "nccl_busbw_gbs": round(bus(nccl), 2),
                **forced}
+        if clk:
+            c = clk.stop()
+            row["clocks"] = {"sm_mhz": c.get("sm_mhz"),
+                             "sm_max_mhz": c.get("sm_max_mhz"),
+                             "reasons": c.get("reasons")}
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)

@@ -161,7 +161,7 @@ class PeerWorkspace:
         votes = comm.allgather((bool(ok), socket.gethostname()))
         if not all(v for v, _ in votes) or len({h for _, h in votes}) != 1:
             return None
-        want = int(os.environ.get("MULTIGRAD_B200_MC_BYTES", 64 << 20))
+        want = int(os.environ.get("MULTIGRAD_B200_MC_BYTES", 128 << 20))
         size = C.c_uint64(0)
         rc = lib.mgb_mc_round_size(world, want, C.byref(size))
         if not all(r == 0 for r in comm.allgather(rc)):
