@@ -53,7 +53,10 @@
 // [0, batch), the others are only used with batch == 1)
 #define EB_RELAY_WORD 32      // host hand-shake relay (token + parameters)
 #define EB_ABORT_WORD 24      // persistent fit: a step failed, everybody leave
-#define EB_DYN_WORD 8         // + group: tile claim counters of the dynamic tail
+#define EB_DYN_WORD 64        // + group*EB_NPOOL + pool: tile claim counters
+#define EB_NPOOL 1            // claim pools per group (8 pools spread the
+                              // atomics but balance worse: measured no gain)
+#define EB_COUNTER_WORDS 256  // minimum size of the counter block
 #ifndef EB_HOST_POLL_NS
 #define EB_HOST_POLL_NS 100
 #endif
@@ -512,7 +515,8 @@ struct EbSched {
   int per_iter;            // G * wpg: tiles the group consumes per iteration
   int static_end;          // tiles [0, static_end) are dealt out statically
   int first;               // this warp's first static tile
-  unsigned* counter;       // claim counter of the group (dynamic tail) or NULL
+  int pool_lo, pool_hi;    // this CTA's pool of dynamic tiles
+  unsigned* counter;       // claim counter of (group, pool) or NULL
 };
 
 __device__ __forceinline__ EbSched eb_make_sched(const MgbErfBinModel& md,
@@ -524,10 +528,19 @@ __device__ __forceinline__ EbSched eb_make_sched(const MgbErfBinModel& md,
   sc.first = (int)blockIdx.x + wj * (int)gridDim.x;
   sc.static_end = sc.ntiles;
   sc.counter = nullptr;
+  sc.pool_lo = sc.pool_hi = sc.ntiles;
   if (dynamic) {
     sc.static_end =
         (int)(((long long)sc.ntiles * 9 / 10) / sc.per_iter) * sc.per_iter;
-    sc.counter = counter;
+    // the dynamic tiles are split into EB_NPOOL contiguous pools with a
+    // counter each (one counter for all would see an atomic every 1.7 ns);
+    // CTA c claims from pool c % EB_NPOOL
+    const int pool = (int)(blockIdx.x % EB_NPOOL);
+    const int dyn = sc.ntiles - sc.static_end;
+    const int per = ((dyn + EB_NPOOL - 1) / EB_NPOOL + 1) & ~1;
+    sc.pool_lo = min(sc.static_end + pool * per, sc.ntiles);
+    sc.pool_hi = min(sc.pool_lo + per, sc.ntiles);
+    sc.counter = counter + pool;
   }
   return sc;
 }
@@ -561,9 +574,9 @@ __device__ __forceinline__ void accumulate_group(
     unsigned cl = 0;
     if (lane == 0) cl = atomicAdd(sc.counter, 1u);
     cl = __shfl_sync(0xffffffffu, cl, 0);
-    const unsigned t3 = (unsigned)sc.static_end + 2u * cl;
-    if (t3 >= (unsigned)sc.ntiles) return -1;
-    second = (t3 + 1u < (unsigned)sc.ntiles) ? (int)t3 + 1 : -1;
+    const unsigned t3 = (unsigned)sc.pool_lo + 2u * cl;
+    if (t3 >= (unsigned)sc.pool_hi) return -1;
+    second = (t3 + 1u < (unsigned)sc.pool_hi) ? (int)t3 + 1 : -1;
     return (int)t3;
   };
   int cur = sc.first;
@@ -738,10 +751,10 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
   const int wpg = lay.w0[grp + 1] - lay.w0[grp];
   const int wj = warp - lay.w0[grp];
   // dynamic tail (unless MGB_STEP_STATIC_SPLIT): claim counters are words
-  // EB_DYN_WORD + group of the counter block (batch == 1 only)
+  // EB_DYN_WORD + group*EB_NPOOL + pool of the counter block (batch == 1)
   const EbSched sched = eb_make_sched(
       md, wj, wpg, (a.flags & MGB_STEP_STATIC_SPLIT) == 0 && gridDim.y == 1,
-      counters + EB_DYN_WORD + grp);
+      counters + EB_DYN_WORD + grp * EB_NPOOL);
 
   // Programmatic dependent launch: this grid may have been scheduled while
   // the previous step's last CTA was still in its epilogue (launch latency and
@@ -988,7 +1001,7 @@ erfbin_step_kernel(const __grid_constant__ MgbErfBinModel md,
     mgb_grid_reduce_f64(partials + (size_t)b * NC * MP, NC, MP, sh.tot, tid,
                         nthreads);
     if (tid == 0) counters[b] = 0u;  // ready for the next step / launch
-    if (sched.counter != nullptr && tid < lay.ng)
+    if (sched.counter != nullptr && tid < lay.ng * EB_NPOOL)
       counters[EB_DYN_WORD + tid] = 0u;
     __syncthreads();
     if (a.trace && tid == 0) tr2 = mgb_globaltimer_ns();
@@ -1278,6 +1291,13 @@ int pick_cluster(eb_kernel_t k, int grid, int block, int* out) {
 
 }  // namespace
 
+// size of the counter block in front of the partial sums: one ticket word per
+// batch entry, at least EB_COUNTER_WORDS words (relay, abort and claim words)
+static uint64_t eb_counter_bytes(int batch) {
+  const uint64_t b = ((uint64_t)batch * 4ull + 255ull) & ~255ull;
+  return b < 4ull * EB_COUNTER_WORDS ? 4ull * EB_COUNTER_WORDS : b;
+}
+
 // cluster size the fused step will be launched with (diagnostics)
 extern "C" int mgb_erfbin_cluster(int nbins, int weighted) {
   if (nbins < 1 || nbins > MGB_MAX_BINS) return 0;
@@ -1303,8 +1323,7 @@ extern "C" int mgb_erfbin_grid(int nbins) {
 extern "C" uint64_t mgb_erfbin_scratch_bytes(int nbins, int batch) {
   if (nbins < 1 || nbins > MGB_MAX_BINS || batch < 1) return 0;
   const int grid = grid_for(nbins);
-  const uint64_t counters = ((uint64_t)batch * 4ull + 255ull) & ~255ull;
-  return counters + (uint64_t)batch * grid * 3ull * nbins * 8ull;
+  return eb_counter_bytes(batch) + (uint64_t)batch * grid * 3ull * nbins * 8ull;
 }
 
 extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
@@ -1388,7 +1407,7 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
   MGB_REQUIRE(scratch_bytes >= need, MGB_ETOOBIG,
               "mgb_erfbin_step: scratch %llu < %llu bytes",
               (unsigned long long)scratch_bytes, (unsigned long long)need);
-  const uint64_t coff = ((uint64_t)a.batch * 4ull + 255ull) & ~255ull;
+  const uint64_t coff = eb_counter_bytes(a.batch);
   unsigned* counters = reinterpret_cast<unsigned*>(scratch);
   double* partials =
       reinterpret_cast<double*>(reinterpret_cast<char*>(scratch) + coff);
@@ -1515,8 +1534,7 @@ extern "C" int mgb_erfbin_step_static(const MgbErfBinModel* model,
   const int rc = static_scratch_address(&scratch);
   if (rc != MGB_OK) return rc;
   // the ticket counters must start at zero; the partial sums are overwritten
-  const uint64_t counter_bytes =
-      ((uint64_t)args->batch * 4ull + 255ull) & ~255ull;
+  const uint64_t counter_bytes = eb_counter_bytes(args->batch);
   MGB_CUDA_CHECK(
       cudaMemsetAsync(scratch, 0, counter_bytes, (cudaStream_t)stream));
   return mgb_erfbin_step(model, args, pt, scratch, MGB_STATIC_SCRATCH_BYTES,
@@ -1675,7 +1693,7 @@ extern "C" int mgb_erfbin_adam_host(
   a.wait_timeout_ms = timeout_ms;
   int rc = MGB_OK;
   // the device-side relay of the hand-shake starts from zero
-  MGB_REQUIRE(scratch != nullptr && scratch_bytes >= 256, MGB_EINVAL,
+  MGB_REQUIRE(scratch != nullptr && scratch_bytes >= 4 * EB_COUNTER_WORDS, MGB_EINVAL,
               "mgb_erfbin_adam_host: scratch missing");
   MGB_CUDA_CHECK(cudaMemsetAsync(
       reinterpret_cast<char*>(scratch) + 4 * EB_RELAY_WORD, 0,
@@ -1794,7 +1812,7 @@ extern "C" int mgb_erfbin_host_session(
     float* out_host, void* scratch, uint64_t scratch_bytes, void* stream,
     uint32_t timeout_ms, int32_t op, uint32_t* seq) {
   MGB_REQUIRE(model && params_host && out_host && seq && scratch &&
-                  scratch_bytes >= 256,
+                  scratch_bytes >= 4 * EB_COUNTER_WORDS,
               MGB_EINVAL, "mgb_erfbin_host_session: bad arguments");
   const int P = model->nparams;
   MGB_REQUIRE(P >= 1 && P <= MGB_MAX_PARAMS, MGB_ETOOBIG,
