@@ -54,12 +54,17 @@ def main():
         plan.launch(a)
     torch.cuda.synchronize()
     comm.Barrier()
+    from bench import ClockSampler
+    clk = ClockSampler(comm.size) if comm.rank == 0 else None
+    if clk:
+        clk.start()
     e0, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
     e0.record()
     for _ in range(args.steps):
         plan.launch(a)
     e1.record()
     torch.cuda.synchronize()
+    clocks = clk.stop() if clk else None
     ms = max(comm.allgather(e0.elapsed_time(e1) / args.steps))
     model._check()
     bytes_per_gpu = n * (plan.pfeat * 2 + 4)
@@ -76,7 +81,9 @@ def main():
             "halos_total": n_tot, "features": F, "pfeat": plan.pfeat,
             "ms_per_step": ms, "steps_per_sec": 1e3 / ms,
             "hbm_gbs_per_gpu": gbs, "frac_of_measured_copy_bw": gbs / peak,
-            "final_loss": float(st.loss_hist[int(st.step.item()) - 1])}))
+            "final_loss": float(st.loss_hist[int(st.step.item()) - 1]),
+            "l2": "inputs>L2" if bytes_per_gpu > (126 << 20) else "resident",
+            "clocks": clocks}))
     mg.shutdown()
 
 

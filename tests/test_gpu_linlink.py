@@ -137,3 +137,28 @@ def test_constant_feature_reproduces_smf_model():
     assert torch.allclose(g1, g2, rtol=1e-4, atol=1e-6)
     assert torch.allclose(data["target_sumstats"],
                           lin.calc_sumstats_from_params([-2.0, 0.2]))
+
+
+def test_fp8_gate_decision_is_reproducible():
+    """The FP8 gate (tools/fp8_gate.py): MXFP8 features are emulated exactly
+    on the bf16 kernel; the committed decision (profiles/linlink_fp8_gate.json)
+    must be the one this measurement gives."""
+    import json
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parents[1]
+    sys.path.insert(0, str(root / "tools"))
+    import fp8_gate
+    # the emulation is exact: dequantised MXFP8 values survive bf16
+    w = 0.3 * torch.randn(64, 64)
+    q = fp8_gate.mxfp8_dequant(w)
+    assert torch.equal(q, q.to(torch.bfloat16).float())
+    assert float((q - w).abs().max()) < 0.07 * float(w.abs().max())
+    res = fp8_gate.run(100_000, 64)
+    assert res["bf16"]["jacobian_rel_err"] < 2e-4
+    accepted = res["mxfp8"]["jacobian_rel_err"] <= fp8_gate.JAC_TOL
+    rec = root / "profiles" / "linlink_fp8_gate.json"
+    if rec.exists():
+        lines = [json.loads(l) for l in rec.read_text().splitlines() if l]
+        assert all(l["decision"].startswith("accepted") == accepted
+                   for l in lines), (res, lines)

@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""FP8 gate of the tensor-core linear-link family (north star: "block-scaled
+fp8 inputs only where accuracy tests allow").
+
+The candidate: store the feature matrix W as MXFP8 -- e4m3 elements with one
+power-of-two (UE8M0) scale per block of 32 features of an object, the operand
+format of ``tcgen05.mma.kind::mxf8f6f4.block_scale`` -- which would halve the
+HBM traffic of a kernel that is HBM-bound on W.
+
+The decision needs no FP8 kernel: an e4m3 value times a power of two is
+exactly representable in bf16, and the UMMA accumulates in fp32 either way, so
+running the existing bf16 kernel on the *dequantised* W produces bit for bit
+the products an MXFP8 UMMA would produce.  (This is the optimistic case: the
+second operand -- theta planes / Gaussian weights -- is left in bf16, although
+kind::mxf8f6f4 would need it in 8 bits too.)  The gate compares statistic and
+Jacobian against the float64 oracle on the ORIGINAL features and accepts only
+if the Jacobian stays within 2e-3 relative (of its largest entry).
+
+    python tools/fp8_gate.py [objects] [features]       -> one JSON line
+"""
+import json
+import sys
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import numpy as np
+import torch
+import multigrad_b200 as mg
+from multigrad_b200.models import LinearLinkBinnedModel
+
+JAC_TOL = 2e-3
+
+
+def mxfp8_dequant(w: torch.Tensor, block: int = 32) -> torch.Tensor:
+    """Round ``w [n, F]`` to MXFP8 (e4m3, shared UE8M0 scale per ``block``
+    features) and return the dequantised values (exact in bf16)."""
+    n, F = w.shape
+    pad = (-F) % block
+    wp = torch.nn.functional.pad(w.float(), (0, pad)).reshape(n, -1, block)
+    amax = wp.abs().amax(dim=2, keepdim=True).clamp_min(2.0 ** -126)
+    # largest power of two such that amax / scale <= 448 (e4m3 max)
+    scale = torch.exp2(torch.ceil(torch.log2(amax / 448.0)))
+    q = (wp / scale).to(torch.float8_e4m3fn).float() * scale
+    return q.reshape(n, -1)[:, :F]
+
+
+def run(n=200_000, F=64, seed=0):
+    dev = torch.device("cuda", 0)
+    SELF = mg.Comm(None)
+    g = torch.Generator().manual_seed(seed)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    feat = torch.cat([torch.ones(n, 1),
+                      0.3 * torch.randn(n, F - 1, generator=g)], 1)
+    feat = feat.to(torch.bfloat16).float()          # the bf16 baseline inputs
+    edges = np.linspace(9.0, 10.0, 11)
+    theta = torch.cat([torch.tensor([-2.0]),
+                       0.05 * torch.randn(F - 1, generator=g),
+                       torch.tensor([0.2])])
+    kw = dict(bin_edges=edges, volume=10.0 * n, comm=SELF)
+    cpu = LinearLinkBinnedModel(x=x.double(), features=feat, device="cpu",
+                                **kw)
+    so = cpu.calc_partial_sumstats_from_params(theta.double())
+    jo = torch.autograd.functional.jacobian(
+        lambda q: cpu.calc_partial_sumstats_from_params(q), theta.double())
+    out = {}
+    for name, w in (("bf16", feat), ("mxfp8", mxfp8_dequant(feat))):
+        m = LinearLinkBinnedModel(x=x.to(dev), features=w.to(dev), device=dev,
+                                  **kw)
+        s, jac = m.calc_sumstats_and_jac_from_params(theta)
+        out[name] = {
+            "sumstats_rel_err": float(((s.double().cpu() - so).abs()
+                                       / so.abs()).max()),
+            "jacobian_rel_err": float((jac.double().cpu() - jo).abs().max()
+                                      / jo.abs().max())}
+    q = mxfp8_dequant(feat)
+    out["feature_rel_rounding_rms"] = float(
+        ((q - feat)[:, 1:] ** 2).mean().sqrt() / (feat[:, 1:] ** 2).mean()
+        .sqrt())
+    ok = out["mxfp8"]["jacobian_rel_err"] <= JAC_TOL
+    out.update(objects=n, features=F, jacobian_tolerance=JAC_TOL,
+               decision="accepted" if ok else
+               f"rejected: MXFP8 features put the Jacobian "
+               f"{out['mxfp8']['jacobian_rel_err']:.1e} off (tolerance "
+               f"{JAC_TOL:.0e}; bf16: {out['bf16']['jacobian_rel_err']:.1e})")
+    return out
+
+
+if __name__ == "__main__":
+    n = int(float(sys.argv[1])) if len(sys.argv) > 1 else 200_000
+    F = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+    print(json.dumps(run(n, F)))
