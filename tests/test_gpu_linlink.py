@@ -156,7 +156,9 @@ def test_fp8_gate_decision_is_reproducible():
     assert float((q - w).abs().max()) < 0.07 * float(w.abs().max())
     res = fp8_gate.run(100_000, 64)
     assert res["bf16"]["jacobian_rel_err"] < 2e-4
-    accepted = res["mxfp8"]["jacobian_rel_err"] <= fp8_gate.JAC_TOL
+    accepted = (res["mxfp8"]["jacobian_rel_err"] <= fp8_gate.JAC_TOL and
+                res["mxfp8"]["sumstats_rel_err"] <= fp8_gate.SUM_TOL)
+    assert res["decision"].startswith("accepted") == accepted
     rec = root / "profiles" / "linlink_fp8_gate.json"
     if rec.exists():
         lines = [json.loads(l) for l in rec.read_text().splitlines() if l]
