@@ -14,7 +14,7 @@ cuobjdump -sass "$LIB" > "$TMP"
 {
   echo "# SASS evidence (tools/sass_evidence.sh: cuobjdump -sass $LIB), sm_100a"
   echo "## instruction counts over the whole library"
-  grep -oE "UTCHMMA|UTCBAR|UTCATOMSWS|LDTM|UTMALDG|LDGMC[.A-Z0-9x]*|MUFU\.(EX2|RCP)|FFMA2|FMUL2|FADD2|SYNCS\.[A-Z]+\.|ACQBULK|CCTL[.A-Z]*|REDG[.A-Z0-9]*|ST[GS]?\.E\.[A-Z0-9.]*MMIO[.A-Z]*|RED\.E\.[.A-Z0-9]*|MULTIMEM[.A-Z0-9]*" "$TMP" | sort | uniq -c
+  grep -oE "UCGABAR_ARV|UCGABAR_WAIT|UTCHMMA|UTCBAR|UTCATOMSWS|LDTM|UTMALDG|LDGMC[.A-Z0-9x]*|MUFU\.(EX2|RCP)|FFMA2|FMUL2|FADD2|SYNCS\.[A-Z]+\.|ACQBULK|CCTL[.A-Z]*|REDG[.A-Z0-9]*|ST[GS]?\.E\.[A-Z0-9.]*MMIO[.A-Z]*|RED\.E\.[.A-Z0-9]*|MULTIMEM[.A-Z0-9]*" "$TMP" | sort | uniq -c
   for k in "linlink_step_kernelILi64" "nvls_allreduce_f32_kernelILb1" "oneshot_allreduce_f32_kernel" "group_step_kernel"; do
     echo
     echo "## $k: tensor-core / TMA / TMEM / multimem instructions and system-scope (peer) accesses"
@@ -22,9 +22,15 @@ cuobjdump -sass "$LIB" > "$TMP"
       grep -E "UTCHMMA|UTCBAR|LDTM|UTMALDG|LDGMC|STRONG\.SYS|MULTIMEM|REDG|\.MMIO" | head -40
   done
   echo
-  echo "## erfbin_step_kernel<4,false>: packed fp32 main loop (excerpt), PDL, and the system-scope LL accesses"
-  awk '/Function :/ {on = index($0, "erfbin_step_kernelILi4ELb0") > 0} on' "$TMP" |
-    grep -E "FFMA2|FMUL2|FADD2|MUFU|STRONG\.SYS|ACQBULK|DEPBAR|PREEXIT|LDG.*CONSTANT" | head -60
+  echo "## erfbin_step_kernel<11,false>: thread-block cluster / DSMEM reduction (barrier.cluster = UCGABAR_*,"
+  echo "## %cluster_ctarank = SR_CgaCtaId, mapa = PRMT 0x654 on the shared address, st.shared::cluster = ST.E.64),"
+  echo "## persistent-fit hand-over (LDG/STG.STRONG.GPU on the step counter), tile claims (ATOMG), PDL (ACQBULK/PREEXIT)"
+  awk '/Function :/ {on = index($0, "erfbin_step_kernelILi11ELb0") > 0} on' "$TMP" |
+    grep -E "UCGABAR|SR_Cga|PRMT.*0x654|ST\.E\.64 |STRONG\.GPU|ATOMG|ACQBULK|PREEXIT|CCTL" | head -40
+  echo
+  echo "## erfbin_step_kernel<11,false>: packed fp32 main loop (excerpt) and the system-scope LL accesses"
+  awk '/Function :/ {on = index($0, "erfbin_step_kernelILi11ELb0") > 0} on' "$TMP" |
+    grep -E "FFMA2|FMUL2|FADD2|MUFU|STRONG\.SYS|LDG.*CONSTANT" | head -60
 } > "$OUT"
 rm -f "$TMP"
 wc -l "$OUT"
