@@ -39,7 +39,7 @@ __device__ long long g_ll_trace[8][LL_TRACE_N];
     if (blockIdx.x == 0 && _t >= 0 && _t < LL_TRACE_N)                        \
       g_ll_trace[ev][_t] = clock64();                                         \
   } while (0)
-__device__ long long g_ll_trace_w[24][2][LL_TRACE_N];   // per compute warp
+__device__ long long g_ll_trace_w[32][2][LL_TRACE_N];   // per compute warp
 #define LL_TRW(cw, ev, tile)                                                  \
   do {                                                                        \
     const long long _t = (tile) - LL_TRACE_T0;                                \
@@ -287,28 +287,61 @@ __host__ __device__ constexpr int ll_nacc(int) { return LL_NACC_SWAP; }
 #else
 __host__ __device__ constexpr int ll_nacc(int P) { return P <= 64 ? 4 : 2; }
 #endif
-constexpr int LL_SETS = 2;          // compute-warp sets; set k owns tiles it%2==k
-constexpr int LL_CWARPS = 12;       // compute warps per set
-constexpr int LL_THREADS = 32 * (2 + LL_SETS * LL_CWARPS);   // 832
-constexpr int LL_ET = 4;            // edges per compute group (3 groups)
+// Compute-warp layout.  A tile is worked on by 4 * groups warps (one per TMEM
+// lane quadrant and edge group); a warp owns LL_CH * nch edges of its 32
+// objects; `sets` tiles are in the compute phase at the same time (set k owns
+// tiles it % sets == k).  Few warps with many edges each amortise the
+// per-tile hand-shakes (two barrier waits, tcgen05.ld, proxy fence, arrive)
+// and give every warp nch * LL_CH independent chains.
+#ifndef LL_CH
+#define LL_CH 4
+#endif
+#ifndef LL_NCH64
+#define LL_NCH64 3
+#endif
+#ifndef LL_SETS64
+#define LL_SETS64 4
+#endif
+#ifndef LL_NCH128
+#define LL_NCH128 3
+#endif
+#ifndef LL_SETS128
+#define LL_SETS128 3
+#endif
 constexpr int LL_MAXE = MGB_LIN_MAX_BINS + 1;
+__host__ __device__ constexpr int ll_nch(int P) {
+  return P <= 64 ? LL_NCH64 : LL_NCH128;
+}
+__host__ __device__ constexpr int ll_sets(int P) {
+  return P <= 64 ? LL_SETS64 : LL_SETS128;
+}
+__host__ __device__ constexpr int ll_groups(int P) {
+  return (LL_MAXE + LL_CH * ll_nch(P) - 1) / (LL_CH * ll_nch(P));
+}
+__host__ __device__ constexpr int ll_threads(int P) {
+  return 32 * (2 + ll_sets(P) * 4 * ll_groups(P));
+}
+constexpr int LL_MAX_CWARPS = 30;
 constexpr float LL_KAPPA = 1.2011224087864498f;
 constexpr float LL_HSCALE = MGB_ERFCX_CSCALE / LL_KAPPA;
 
 struct LinSmemLayout {
-  int w_bytes, th_off, g_off, total;
+  int w_bytes, th_off, g_off, x_off, total;
 };
+// per stage: 128 floats of x, then 128 floats of per-object weights
+constexpr int LL_XSTAGE = 2 * LL_TILE * 4;
 __host__ __device__ inline LinSmemLayout lin_smem_layout(int P) {
   LinSmemLayout L;
   L.w_bytes = (P / LL_FB) * LL_TILE * 128;          // per stage
   L.th_off = ll_stages(P) * L.w_bytes;
   L.g_off = L.th_off + (P / LL_FB) * 2048;
-  L.total = L.g_off + ll_stages(P) * 8192 + 16384;  // + UMMA over-read slack
+  L.x_off = L.g_off + ll_stages(P) * 8192;
+  L.total = L.x_off + 16384;   // x / weight stages (<= 8 KiB) + spare
   return L;
 }
 
-template <int P>
-__global__ void __launch_bounds__(LL_THREADS, 1)
+template <int P, bool WEIGHTED>
+__global__ void __launch_bounds__(ll_threads(P), 1)
 linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
                     const MgbLinModel md, const MgbLinArgs a,
                     const MgbPeerTable pt, double* __restrict__ partials,
@@ -319,6 +352,11 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   uint8_t* s_w = smem;
   uint8_t* s_th = smem + L.th_off;
   uint8_t* s_g = smem + L.g_off;
+  // x (and weights) of a tile travel with its W tile: a 512-byte bulk copy on
+  // the same mbarrier.  (Loading them with LDG from the compute warps put a
+  // global-load latency in front of every G hand-over: the releasing
+  // mbarrier.arrive drains the thread's outstanding loads first.)
+  const float* s_xf = reinterpret_cast<const float*>(smem + L.x_off);
 
   constexpr int LL_STAGES = ll_stages(P);
   constexpr int NACC = ll_nacc(P);
@@ -326,7 +364,13 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       g_full[LL_MAX_STAGES], empty[LL_MAX_STAGES], d2_done;
   __shared__ uint32_t s_tmem;
   __shared__ float s_cs[LL_MAXE];
-  __shared__ double s_warp[LL_SETS * LL_CWARPS][3 * LL_ET];
+  constexpr int LL_THREADS = ll_threads(P);
+  constexpr int SETS = ll_sets(P), NCH = ll_nch(P), GROUPS = ll_groups(P);
+  constexpr int EPW = LL_CH * NCH;        // edges per compute warp
+  constexpr int CWS = 4 * GROUPS;         // compute warps per set (= per tile)
+  static_assert(SETS * CWS <= LL_MAX_CWARPS && LL_THREADS <= 1024, "layout");
+  static_assert(SETS <= ll_stages(P) - 1, "a stage must be left for the TMA");
+  __shared__ double s_warp[SETS * CWS][3 * EPW];
   __shared__ double s_edge[LL_MAXE][3];
   __shared__ int s_is_last, s_fail;
 
@@ -359,7 +403,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
     for (int s = 0; s < LL_STAGES; ++s) {
       mbar_init(&full_w[s], 1);
       mbar_init(&mu_full[s], 1);
-      mbar_init(&g_full[s], LL_CWARPS);
+      mbar_init(&g_full[s], CWS);
       mbar_init(&empty[s], 1);
     }
     mbar_init(&d2_done, 1);
@@ -391,10 +435,20 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         if (!mbar_wait(&empty[s], ph ^ 1u)) { fail = 1; break; }
         LL_TR(0, it);
         const long long tile = tile0 + it * tstride;
-        mbar_arrive_expect_tx(&full_w[s], (uint32_t)L.w_bytes);
+        // a ragged last tile reads x / weights with plain loads instead
+        const bool whole = (tile + 1) * LL_TILE <= md.n;
+        const uint32_t xb = whole ? (WEIGHTED ? 2u : 1u) * (LL_TILE * 4) : 0u;
+        mbar_arrive_expect_tx(&full_w[s], (uint32_t)L.w_bytes + xb);
         for (int fb = 0; fb < NFB; ++fb)
           tma_load_2d(s_w + s * L.w_bytes + fb * LL_TILE * 128, &wmap,
                       &full_w[s], fb * LL_FB, (int)(tile * LL_TILE));
+        if (whole) {
+          uint8_t* xs = smem + L.x_off + s * LL_XSTAGE;
+          bulk_load(xs, md.x + tile * LL_TILE, LL_TILE * 4, &full_w[s]);
+          if (WEIGHTED)
+            bulk_load(xs + LL_TILE * 4, md.ow + tile * LL_TILE, LL_TILE * 4,
+                      &full_w[s]);
+        }
       }
     }
   } else if (warp == 1) {
@@ -506,50 +560,69 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   } else {
     // ------------------------------------------------------ compute warps
     const int cw = warp - 2;
-    const int set = cw / LL_CWARPS;      // which tiles (it % LL_SETS == set)
-    const int grp = (cw % LL_CWARPS) >> 2;   // edge group
+    const int set = cw / CWS;            // which tiles (it % SETS == set)
+    const int grp = (cw % CWS) >> 2;     // edge group
     const int quad = warp & 3;           // TMEM lane quadrant this warp owns
     const int o = quad * 32 + lane;      // object within the tile
-    const int e_first = grp * LL_ET;
-    float cs[LL_ET];
-    float accT[LL_ET], accZ[LL_ET];
-    int accO[LL_ET];
+    const int e_first = grp * EPW;
+    float cs[EPW];
+    float accT[EPW], accZ[EPW];
+    float accO[EPW];   // weighted: weight below the edge; else an int32 count
+    uint32_t goff[EPW];
+    // G word of this lane: even lanes store the g_hi pair of columns
+    // (ko, ko+1) into row `edge`, odd lanes the g_lo pair into row
+    // 16 + (edge ^ 4) (conflict-free: the ^4 moves the lo word four 16-byte
+    // chunks away from the hi word inside the SW128 pattern)
+    const bool odd = lane & 1;
+    const uint32_t ko = (uint32_t)o & 63u;
+    const uint32_t perm = odd ? 0x1054u : 0x7632u;
 #pragma unroll
-    for (int e = 0; e < LL_ET; ++e) {
+    for (int e = 0; e < EPW; ++e) {
+      const uint32_t r = (uint32_t)(e_first + e);
       cs[e] = (e_first + e < E) ? s_cs[e_first + e] : 3.0e18f;
-      accT[e] = 0.f; accZ[e] = 0.f; accO[e] = 0;
+      accT[e] = 0.f; accZ[e] = 0.f;
+      accO[e] = WEIGHTED ? 0.f : __int_as_float(0);
+      goff[e] = sw128_offset_16b(odd ? 16u + (r ^ 4u) : r, ko & ~1u) +
+                (uint32_t)(o >> 6) * 4096u;
     }
     long long obj = (tile0 + (long long)set * tstride) * LL_TILE + o;
-    float xn = (set < my_tiles && obj < md.n && !(LL_ABL & 16))
-                   ? __ldg(md.x + obj) : 1.0e30f;
-    for (long long it = set; it < my_tiles; it += LL_SETS) {
+    for (long long it = set; it < my_tiles; it += SETS) {
       const int s = (int)(it % LL_STAGES);
       const uint32_t ph = (uint32_t)((it / LL_STAGES) & 1);
-      const float xv = xn;
       const bool valid = obj < md.n;
-      obj += (long long)LL_SETS * tstride * LL_TILE;
-      if (it + LL_SETS < my_tiles)
-        xn = (obj < md.n && !(LL_ABL & 16)) ? __ldg(md.x + obj) : 1.0e30f;
+      const bool whole = obj - o + LL_TILE <= md.n;     // warp-uniform
       if (grp == 0 && quad == 0 && lane == 0) LL_TR(5, it);
+      // the tile's own barrier first: it is what makes the bulk-copied x
+      // visible to this thread (long complete by the time mu is there)
+      if (!mbar_wait(&full_w[s], ph)) { fail = 1; break; }
+      float xv = 1.0e30f, wv = 0.0f;
+      if (!(LL_ABL & 16)) {
+        if (whole) {
+          xv = s_xf[s * (LL_XSTAGE / 4) + o];
+          if (WEIGHTED) wv = s_xf[s * (LL_XSTAGE / 4) + LL_TILE + o];
+        } else if (valid) {
+          xv = __ldg(md.x + obj);
+          if (WEIGHTED) wv = __ldg(md.ow + obj);
+        }
+      }
+      obj += (long long)SETS * tstride * LL_TILE;
       if (!mbar_wait(&mu_full[s], ph)) { fail = 1; break; }
       if (grp == 0 && quad == 0 && lane == 0) LL_TR(2, it);
       if (lane == 0) LL_TRW(cw, 0, it);
       tc_fence_after();
-      uint32_t v[8];
+      uint32_t v[4];
       if (LL_ABL & 32) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = 0u;
+        for (int i = 0; i < 4; ++i) v[i] = 0u;
       } else {
-        tmem_ld_x8(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
+        tmem_ld_x4(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
         tmem_ld_wait();
       }
       const float muf = (__uint_as_float(v[0]) + __uint_as_float(v[1])) +
                         __uint_as_float(v[2]);
       // u = (x - x0) + W.theta ; zs_e = cs_e - ks*u
       const float u = valid ? (xv - x0) + muf : 1.0e30f;
-      uint8_t* gs = s_g + s * 8192 + (o >> 6) * 4096;
-      const uint32_t ko = o & 63;
-      float zs[LL_ET], t[LL_ET], g[LL_ET], pp[LL_ET];
+      uint8_t* gs = s_g + s * 8192;
       if (LL_ABL & 4) {            // no math, no G stores: hand the tile on
         accT[0] += u;
         if (!(LL_ABL & 64)) fence_proxy_async_smem();
@@ -559,51 +632,62 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         continue;
       }
 #pragma unroll
-      for (int e = 0; e < LL_ET; ++e) zs[e] = fmaf(u, -ks, cs[e]);
+      for (int c = 0; c < NCH; ++c) {
+        // chunks past the last edge are skipped (warp-uniform); their G rows
+        // feed accumulator columns nobody reads
+        if (e_first + c * LL_CH >= E) break;
+        float zs[LL_CH], t[LL_CH], g[LL_CH], pp[LL_CH];
 #pragma unroll
-      for (int e = 0; e < LL_ET; ++e)
-        t[e] = mgb_rcp(fmaf(fabsf(zs[e]), LL_HSCALE, 1.0f));
+        for (int k = 0; k < LL_CH; ++k)
+          zs[k] = fmaf(u, -ks, cs[c * LL_CH + k]);
 #pragma unroll
-      for (int e = 0; e < LL_ET; ++e) g[e] = mgb_ex2(-(zs[e] * zs[e]));
-      constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
+        for (int k = 0; k < LL_CH; ++k)
+          t[k] = mgb_rcp(fmaf(fabsf(zs[k]), LL_HSCALE, 1.0f));
 #pragma unroll
-      for (int e = 0; e < LL_ET; ++e)
-        pp[e] = fmaf(0.5f * kC[MGB_ERFCX_DEG], t[e],
-                     0.5f * kC[MGB_ERFCX_DEG - 1]);
+        for (int k = 0; k < LL_CH; ++k) {
+          g[k] = mgb_ex2(-(zs[k] * zs[k]));
+          if (WEIGHTED) g[k] *= wv;      // the weight rides on the Gaussian
+        }
+        constexpr float kC[MGB_ERFCX_DEG + 1] = MGB_ERFCX_COEFFS;
 #pragma unroll
-      for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
+        for (int k = 0; k < LL_CH; ++k)
+          pp[k] = fmaf(0.5f * kC[MGB_ERFCX_DEG], t[k],
+                       0.5f * kC[MGB_ERFCX_DEG - 1]);
 #pragma unroll
-        for (int e = 0; e < LL_ET; ++e)
-          pp[e] = fmaf(pp[e], t[e], 0.5f * kC[d]);
-      }
+        for (int d = MGB_ERFCX_DEG - 2; d >= 0; --d) {
 #pragma unroll
-      for (int e = 0; e < LL_ET; ++e) {
-        const float q = pp[e] * t[e] * g[e];
-        accT[e] += __uint_as_float(__float_as_uint(q) |
-                                   (~__float_as_uint(zs[e]) & 0x80000000u));
-        accO[e] += (int)(__float_as_uint(zs[e]) >> 31);
-        accZ[e] = fmaf(zs[e], g[e], accZ[e]);
-        // g -> two bf16 planes, column = object: the hi plane in row `edge`,
-        // the lo plane in row 16 + (edge ^ 4).  The ^4 moves the lo word of a
-        // lane pair four 16-byte chunks away from the hi word inside the
-        // SW128 pattern; with 16 + edge both land in the same bank (rows 16
-        // apart share r % 8) and every store is a 2-way conflict (ncu: 52% of
-        // the shared-store wavefronts were conflicts).
-        // Lanes pair up so that every lane issues one full-word store: the
-        // even lane writes the g_hi pair, the odd lane the g_lo pair
-        // (2-byte stores from all 32 lanes cost 3x the wavefronts; ncu).
-        const float ghi = bf16_val(g[e]);
-        const uint32_t mine = ((uint32_t)bf16_bits(ghi) << 16) |
-                              (uint32_t)bf16_bits(g[e] - ghi);
-        const uint32_t other = __shfl_xor_sync(0xffffffffu, mine, 1);
-        const uint32_t r = (uint32_t)(e_first + e);
-        const bool odd = lane & 1;
-        // element order in memory: column ko (even lane) then ko+1 (odd lane)
-        const uint32_t word = odd ? ((other & 0xffffu) | (mine << 16))
-                                  : ((mine >> 16) | (other & 0xffff0000u));
-        if (!(LL_ABL & 2))
-          *reinterpret_cast<uint32_t*>(
-              gs + sw128_offset_16b(odd ? 16u + (r ^ 4u) : r, ko & ~1u)) = word;
+          for (int k = 0; k < LL_CH; ++k)
+            pp[k] = fmaf(pp[k], t[k], 0.5f * kC[d]);
+        }
+#pragma unroll
+        for (int k = 0; k < LL_CH; ++k) {
+          const int e = c * LL_CH + k;
+          // T += +q below the edge, -q above, q = pp t g: the sign goes onto
+          // g (sign bit from ~sign(zs)), the product into the FMA
+          const float gsg = __uint_as_float(
+              __float_as_uint(g[k]) | (~__float_as_uint(zs[k]) & 0x80000000u));
+          accT[e] = fmaf(pp[k] * t[k], gsg, accT[e]);
+          if (WEIGHTED) {
+            accO[e] += zs[k] < 0.0f ? wv : 0.0f;
+          } else {
+            accO[e] = __int_as_float(__float_as_int(accO[e]) +
+                                     (int)(__float_as_uint(zs[k]) >> 31));
+          }
+          accZ[e] = fmaf(zs[k], g[k], accZ[e]);
+          // g -> two bf16 planes: hi = g truncated to bf16 (exact), lo =
+          // bf16(g - hi); one cvt packs both.  Lanes pair up so that every
+          // lane issues one full-word store (2-byte stores from all 32 lanes
+          // cost 3x the wavefronts; ncu).
+          const float ghi =
+              __uint_as_float(__float_as_uint(g[k]) & 0xffff0000u);
+          uint32_t mine;
+          asm("cvt.rn.bf16x2.f32 %0, %1, %2;"
+              : "=r"(mine) : "f"(ghi), "f"(g[k] - ghi));
+          const uint32_t other = __shfl_xor_sync(0xffffffffu, mine, 1);
+          if (!(LL_ABL & 2))
+            *reinterpret_cast<uint32_t*>(gs + goff[e]) =
+                __byte_perm(mine, other, perm);
+        }
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -613,13 +697,15 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       if (lane == 0) LL_TRW(cw, 1, it);
     }
 #pragma unroll
-    for (int e = 0; e < LL_ET; ++e) {
+    for (int e = 0; e < EPW; ++e) {
       const float tt = mgb_warp_sum(accT[e]);
       const float zz = mgb_warp_sum(accZ[e]);
-      const int oo = __reduce_add_sync(0xffffffffu, accO[e]);
+      const double oo = WEIGHTED
+          ? (double)mgb_warp_sum(accO[e])
+          : (double)__reduce_add_sync(0xffffffffu, __float_as_int(accO[e]));
       if (lane == 0) {
         s_warp[cw][3 * e + 0] = (double)tt;
-        s_warp[cw][3 * e + 1] = -(double)oo;   // objects below -> sign flip
+        s_warp[cw][3 * e + 1] = -oo;           // objects below -> sign flip
         s_warp[cw][3 * e + 2] = (double)zz;
       }
     }
@@ -630,11 +716,11 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   // ---- per-edge totals of T, O, Z (fp64) ---------------------------------
   for (int j = tid; j < 3 * E; j += LL_THREADS) {
     const int e = j / 3, q = j - 3 * e;
-    const int grp = e / LL_ET, el = e - grp * LL_ET;
+    const int grp = e / EPW, el = e - grp * EPW;
     double sacc = 0.0;
-    for (int st = 0; st < LL_SETS; ++st)
+    for (int st = 0; st < SETS; ++st)
       for (int w = 0; w < 4; ++w)
-        sacc += s_warp[st * LL_CWARPS + grp * 4 + w][3 * el + q];
+        sacc += s_warp[st * CWS + grp * 4 + w][3 * el + q];
     s_edge[e][q] = sacc;
   }
   // ---- D2 (TMEM) -> shared: rows 0..15 g_hi, 16..31 g_lo, P columns -------
@@ -859,8 +945,10 @@ extern "C" int mgb_linlink_step(const MgbLinModel* model,
               "mgb_linlink_step: nfeat=%d outside [1,%d]", md.nfeat, md.pfeat);
   MGB_REQUIRE(md.n >= 0 && md.w && (md.n == 0 || md.x), MGB_EINVAL,
               "mgb_linlink_step: x / w is null");
-  MGB_REQUIRE(((uintptr_t)md.w & 15u) == 0, MGB_EINVAL,
-              "mgb_linlink_step: w must be 16-byte aligned");
+  MGB_REQUIRE(((uintptr_t)md.w & 15u) == 0 && ((uintptr_t)md.x & 15u) == 0 &&
+                  ((uintptr_t)md.ow & 15u) == 0,
+              MGB_EINVAL,
+              "mgb_linlink_step: x, w and ow must be 16-byte aligned");
   MGB_REQUIRE(md.n < (1ll << 31), MGB_ETOOBIG,
               "mgb_linlink_step: n must be below 2^31 objects per GPU");
   MGB_REQUIRE(a.mode >= MGB_MODE_SUMSTATS_JAC && a.mode <= MGB_MODE_GD,
@@ -912,19 +1000,14 @@ extern "C" int mgb_linlink_step(const MgbLinModel* model,
   const int grid = ll_sm_count();
   MGB_REQUIRE(grid > 0, MGB_ESTATE, "mgb_linlink_step: no CUDA device");
   cudaStream_t st = (cudaStream_t)stream;
-  if (md.pfeat == 64) {
-    MGB_CUDA_CHECK(cudaFuncSetAttribute(
-        linlink_step_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int)smem));
-    linlink_step_kernel<64><<<grid, LL_THREADS, smem, st>>>(
-        map, md, a, ptv, partials, counter);
-  } else {
-    MGB_CUDA_CHECK(cudaFuncSetAttribute(
-        linlink_step_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-        (int)smem));
-    linlink_step_kernel<128><<<grid, LL_THREADS, smem, st>>>(
-        map, md, a, ptv, partials, counter);
-  }
+  auto kern = md.pfeat == 64
+      ? (md.ow ? linlink_step_kernel<64, true> : linlink_step_kernel<64, false>)
+      : (md.ow ? linlink_step_kernel<128, true>
+               : linlink_step_kernel<128, false>);
+  MGB_CUDA_CHECK(cudaFuncSetAttribute(
+      kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, ll_threads(md.pfeat), smem, st>>>(map, md, a, ptv, partials,
+                                                 counter);
   MGB_CUDA_CHECK(cudaGetLastError());
   return MGB_OK;
 }

@@ -113,6 +113,16 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst,
       : "memory");
 }
 // generic-proxy writes to smem -> visible to the async proxy (UMMA / TMA)
+// plain (non-tensor) bulk copy global -> shared, completing on an mbarrier;
+// source, destination and size are multiples of 16 bytes
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc,
+                                          uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
@@ -163,6 +173,13 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
 }
 // TMEM -> registers, 32 lanes x 32 bit, 8 / 16 consecutive columns.  Thread i
 // of the warp receives lane (32*(warp%4) + i); v[j] = column (col0 + j).
+__device__ __forceinline__ void tmem_ld_x4(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_x8(uint32_t taddr, uint32_t* v) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"

@@ -336,8 +336,9 @@ int mgb_linkbin_step(const MgbLinkModel* model, const MgbStepArgs* args,
 #define MGB_LIN_MAX_FEAT 128
 
 typedef struct MgbLinModel {
-  const float* x;        /* [n] object coordinate                            */
+  const float* x;        /* [n] object coordinate (16-byte aligned)          */
   const void* w;         /* [n][pfeat] bf16 features                         */
+  const float* ow;       /* [n] per-object weights or NULL (16-byte aligned) */
   int64_t n;
   int32_t nbins;         /* K <= MGB_LIN_MAX_BINS                            */
   int32_t nfeat;         /* features in use (<= pfeat); nparams = nfeat + 1  */

@@ -334,6 +334,7 @@ class OnePointGroup:
         ok = (params.is_cuda and params.numel() <= 8 and all(
             getattr(m, "fused", False) and getattr(m, "_builtin_loss", False)
             and hasattr(m, "device_loss_grad_launcher")
+            and getattr(m, "_one_launch", True)
             and m.device == params.device for m in self.models))
         if self.main_comm is not None and self.main_comm.size > 1:
             ok = all(self.main_comm.allgather(bool(ok)))

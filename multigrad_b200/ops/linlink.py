@@ -11,7 +11,7 @@ from . import _lib
 from .reference import LOSS_KINDS, SIGMA_LINKS
 
 __all__ = ["LinLinkPlan", "LinFitState", "launch_count", "MgbLinModel",
-           "MgbLinArgs"]
+           "MgbLinArgs", "pack_features", "MAX_BINS"]
 
 MAX_BINS = 11
 _LAUNCHES = 0
@@ -23,7 +23,8 @@ def launch_count() -> int:
 
 class MgbLinModel(C.Structure):
     _fields_ = [
-        ("x", C.c_void_p), ("w", C.c_void_p), ("n", C.c_int64),
+        ("x", C.c_void_p), ("w", C.c_void_p), ("ow", C.c_void_p),
+        ("n", C.c_int64),
         ("nbins", C.c_int32), ("nfeat", C.c_int32), ("pfeat", C.c_int32),
         ("sigma_link", C.c_int32), ("loss_kind", C.c_int32),
         ("loss_eps", C.c_float), ("x0", C.c_float),
@@ -85,13 +86,34 @@ class LinFitState:
         self.loss_hist = torch.zeros(rows, **f32)
 
 
+def pack_features(features: torch.Tensor, device) -> torch.Tensor:
+    """The kernel's feature layout: bf16 ``[n][pfeat]``, ``pfeat`` = 64 or 128,
+    zero padded.  Build it once and hand it to several plans (``packed=``)
+    when one catalogue serves more than one launch plan."""
+    n, nfeat = features.shape
+    if nfeat > 128:
+        raise ValueError("at most 128 features")
+    pfeat = 64 if nfeat <= 64 else 128
+    w = torch.zeros(max(n, 1), pfeat, dtype=torch.bfloat16, device=device)
+    w[:n, :nfeat] = features.detach().to(device).to(torch.bfloat16)
+    return w
+
+
+def _aligned_f32(t: torch.Tensor, device) -> torch.Tensor:
+    t = t.detach().to(device, torch.float32).contiguous()
+    if t.data_ptr() % 16:
+        t = t.clone()
+    return t
+
+
 class LinLinkPlan:
     """Launch plan: features are stored once as bf16 ``[n][pfeat]`` with
-    ``pfeat`` = 64 or 128 (zero padded)."""
+    ``pfeat`` = 64 or 128 (zero padded); optional per-object ``weights``."""
 
     def __init__(self, x: torch.Tensor, features: torch.Tensor, edges, norm,
                  target=None, inv_err=None, sigma_link="identity",
-                 loss="log_mse", loss_eps=0.0, peer_table=None):
+                 loss="log_mse", loss_eps=0.0, peer_table=None, weights=None,
+                 packed: Optional[torch.Tensor] = None):
         if not x.is_cuda:
             raise ValueError("LinLinkPlan needs CUDA tensors")
         self.lib = _lib.load()
@@ -100,14 +122,18 @@ class LinLinkPlan:
         n, nfeat = features.shape
         if x.numel() != n:
             raise ValueError("x and features disagree on the object count")
-        if nfeat > 128:
-            raise ValueError("at most 128 features")
-        pfeat = 64 if nfeat <= 64 else 128
-        x = x.detach().to(self.device, torch.float32).contiguous()
-        w = torch.zeros(max(n, 1), pfeat, dtype=torch.bfloat16,
-                        device=self.device)
-        w[:n, :nfeat] = features.detach().to(self.device).to(torch.bfloat16)
+        w = pack_features(features, self.device) if packed is None else packed
+        pfeat = int(w.shape[1])
+        if (w.dtype != torch.bfloat16 or w.shape[0] != max(n, 1)
+                or pfeat not in (64, 128) or nfeat > pfeat):
+            raise ValueError("packed features do not match (n, nfeat)")
+        x = _aligned_f32(x, self.device)
         self.x, self.w = x, w
+        self.ow = None
+        if weights is not None:
+            if weights.numel() != n:
+                raise ValueError("weights and x disagree on the object count")
+            self.ow = _aligned_f32(weights, self.device)
         edges = np.asarray(edges, dtype=np.float64).ravel()
         K = edges.size - 1
         if K < 1 or K > MAX_BINS:
@@ -115,6 +141,7 @@ class LinLinkPlan:
         self.K, self.nfeat, self.pfeat, self.NP = K, nfeat, pfeat, nfeat + 1
         md = MgbLinModel()
         md.x, md.w, md.n = x.data_ptr(), w.data_ptr(), n
+        md.ow = None if self.ow is None else self.ow.data_ptr()
         md.nbins, md.nfeat, md.pfeat = K, nfeat, pfeat
         md.sigma_link = SIGMA_LINKS[sigma_link]
         md.loss_kind = LOSS_KINDS[loss]

@@ -647,6 +647,68 @@ def gpu_linear_link_world_invariance():
     assert all(b == blobs[0] for b in blobs)
 
 
+@case
+def gpu_linear_link_bfgs_and_group():
+    """Tensor-core linear-link model on several GPUs: weighted objects,
+    replicated L-BFGS-B (same iterate on every rank, close to the float32 CPU
+    fit) and membership of a device-resident OnePointGroup."""
+    if DEV.type != "cuda":
+        return
+    from multigrad_b200.models import LinearLinkBinnedModel
+    from multigrad_b200.ops import group as gp
+    n, F = 30_000, 4
+    g = torch.Generator().manual_seed(11)
+    x = (10.0 + 1.3 * torch.rand(n, generator=g)).float()
+    w = (0.5 + torch.rand(n, generator=g)).float()
+    feat = torch.cat([torch.ones(n, 1), 0.3 * torch.randn(n, F - 1,
+                                                          generator=g)], 1)
+    theta = torch.cat([torch.tensor([-2.0]),
+                       0.05 * torch.randn(F - 1, generator=g),
+                       torch.tensor([0.2])])
+    edges = np.linspace(9, 10, 11)
+    ref = LinearLinkBinnedModel(x=x, features=feat, bin_edges=edges,
+                                volume=10.0 * n, weights=w,
+                                comm=mg.Comm(None), device="cpu")
+    tgt = ref.calc_sumstats_from_params(theta)
+    ref.set_target(tgt)
+    sl = slice(*np.linspace(0, n, SIZE + 1).astype(int)[RANK:RANK + 2])
+    model = LinearLinkBinnedModel(x=x[sl].to(DEV), features=feat[sl].to(DEV),
+                                  weights=w[sl].to(DEV), bin_edges=edges,
+                                  volume=10.0 * n, target_sumstats=tgt)
+    p = theta + 0.04
+    loss, grad = model.calc_loss_and_grad_from_params(p)
+    rl, rg = ref.calc_loss_and_grad_from_params(p)
+    assert torch.allclose(loss.cpu(), rl, rtol=2e-4), (loss, rl)
+    assert torch.allclose(grad.cpu(), rg, rtol=2e-3,
+                          atol=2e-4 * float(rg.abs().max())), (grad, rg)
+    bounds = [(None, None)] * F + [(0.02, 2.0)]
+    res = model.run_bfgs(p, maxsteps=50, param_bounds=bounds)
+    assert res.fun < 1e-3 * float(rl), res
+    blobs = COMM.allgather((np.asarray(res.x).tobytes(), int(res.nfev)))
+    assert all(b == blobs[0] for b in blobs)
+    # group: this model (all ranks) as the only member, device-resident
+    lin2 = LinearLinkBinnedModel(
+        x=x[sl].to(DEV), features=torch.ones(sl.stop - sl.start, 1,
+                                             device=DEV),
+        bin_edges=edges, volume=10.0 * n)
+    lin2.set_target(lin2.calc_sumstats_from_params([-2.0, 0.2]))
+    smf_m = SMFModel(x=x[sl].to(DEV) - 0.02, bin_edges=edges, volume=10.0 * n,
+                     target_sumstats=lin2.target_sumstats)
+    group = mg.OnePointGroup((lin2, smf_m), main_comm=COMM)
+    q = torch.tensor([-1.9, 0.3])
+    assert group._device_ok(q.to(DEV))
+    n0 = gp.launch_count()
+    traj = group.run_adam(q, nsteps=10, learning_rate=0.01)
+    torch.cuda.synchronize()
+    assert gp.launch_count() - n0 == 10
+    want = mg.OnePointModel.run_adam(group, q, nsteps=10, learning_rate=0.01,
+                                     comm=COMM)
+    assert torch.allclose(traj.cpu(), want.cpu(), rtol=5e-5, atol=5e-6), \
+        (traj[-1], want[-1])
+    blobs = COMM.allgather(traj.cpu().numpy().tobytes())
+    assert all(b == blobs[0] for b in blobs)
+
+
 def main():
     only = sys.argv[1:] or list(CASES)
     results = {}

@@ -139,6 +139,125 @@ def test_constant_feature_reproduces_smf_model():
                           lin.calc_sumstats_from_params([-2.0, 0.2]))
 
 
+def make_w(n, F, k=10, seed=3, **kw):
+    g = torch.Generator().manual_seed(seed + 77)
+    w = (0.2 + 1.6 * torch.rand(n, generator=g)).float()
+    gpu, cpu, p = make(n, F, k, seed=seed, **kw)
+    kwg = dict(x=gpu.x, features=gpu.features, bin_edges=gpu._edges64,
+               volume=gpu.volume, sigma_link=gpu.sigma_link, comm=SELF)
+    gw = LinearLinkBinnedModel(weights=w.to(dev()), device=dev(), **kwg)
+    kwc = dict(kwg, x=cpu.x, features=cpu.features)
+    cw = LinearLinkBinnedModel(weights=w.double(), device="cpu", **kwc)
+    return gw, cw, p
+
+
+@pytest.mark.parametrize("n,F,k", [(128, 3, 10), (10_000, 7, 10),
+                                   (50_001, 64, 11), (30_003, 100, 5),
+                                   (5, 2, 1)])
+def test_weighted_objects_vs_fp64(n, F, k):
+    """Per-object weights (whole tiles through the bulk copy, the ragged last
+    tile through plain loads)."""
+    gpu, cpu, p = make_w(n, F, k)
+    s, jac = gpu.calc_sumstats_and_jac_from_params(p)
+    gpu._check()
+    so, jo = oracle(cpu, p)
+    assert torch.allclose(s.double().cpu(), so, rtol=5e-6, atol=1e-12)
+    scale = float(jo.abs().max())
+    assert torch.allclose(jac.double().cpu(), jo, rtol=2e-4,
+                          atol=2e-5 * scale)
+    # unit weights are the unweighted model
+    g1, _, _ = make(n, F, k, seed=3)
+    gu = LinearLinkBinnedModel(
+        x=g1.x, features=g1.features, bin_edges=g1._edges64, volume=g1.volume,
+        weights=torch.ones(n, device=dev()), comm=SELF, device=dev())
+    s1, j1 = g1.calc_sumstats_and_jac_from_params(p)
+    su, ju = gu.calc_sumstats_and_jac_from_params(p)
+    assert torch.allclose(s1, su, rtol=2e-6, atol=1e-12)
+    assert torch.allclose(j1, ju, rtol=1e-5, atol=1e-6 * float(j1.abs().max()))
+
+
+@pytest.mark.parametrize("k", [12, 25, 32])
+def test_more_than_eleven_bins_in_slices(k):
+    gpu, cpu, p = make(40_000, 9, k)
+    assert len(gpu._slices) == -(-k // 11)
+    s, jac = gpu.calc_sumstats_and_jac_from_params(p)
+    gpu._check()
+    so, jo = oracle(cpu, p)
+    assert s.shape == (k,) and jac.shape == (k, 10)
+    assert torch.allclose(s.double().cpu(), so, rtol=5e-6, atol=1e-12)
+    assert torch.allclose(jac.double().cpu(), jo, rtol=2e-4,
+                          atol=2e-5 * float(jo.abs().max()))
+    tgt = gpu.calc_sumstats_from_params(p)
+    gpu.set_target(tgt)
+    cpu.set_target(tgt.cpu())
+    q = p + 0.02
+    loss, grad = gpu.calc_loss_and_grad_from_params(q)
+    q64 = q.double().clone().requires_grad_(True)
+    l64 = cpu.calc_loss_from_sumstats(cpu.calc_partial_sumstats_from_params(q64))
+    (g64,) = torch.autograd.grad(l64, q64)
+    assert abs(float(loss) - float(l64)) < 5e-4 * abs(float(l64))
+    assert torch.allclose(grad.double().cpu(), g64, rtol=2e-3,
+                          atol=2e-4 * float(g64.abs().max()))
+    traj, losses = gpu.run_adam(q, nsteps=15, learning_rate=0.005,
+                                return_loss=True)
+    assert float(losses[-1]) < 0.5 * float(losses[0])
+    l_h, g_h = gpu.loss_and_grad_host(q.numpy())
+    assert abs(l_h - float(loss)) <= 1e-6 * abs(float(loss))
+
+
+def test_host_evaluation_and_bfgs():
+    F = 5
+    gpu, cpu, p = make(60_000, F)
+    tgt = gpu.calc_sumstats_from_params(p)
+    gpu.set_target(tgt)
+    q = p + 0.03
+    from multigrad_b200.ops import linlink as ll
+    n0 = ll.launch_count()
+    l_h, g_h = gpu.loss_and_grad_host(q.numpy())
+    assert ll.launch_count() == n0 + 1          # one launch, no copies
+    loss, grad = gpu.calc_loss_and_grad_from_params(q)
+    assert l_h == float(loss)
+    assert np.array_equal(g_h.astype(np.float32), grad.cpu().numpy())
+    res = gpu.run_bfgs(q, maxsteps=60,
+                       param_bounds=[(None, None)] * F + [(0.02, 2.0)])
+    assert res.fun < 1e-3 * l_h, res
+    # host-state Adam walks the device-state trajectory
+    th, lh = gpu.run_adam_host(q, nsteps=12, learning_rate=0.01,
+                               return_loss=True)
+    td, ld = gpu.run_adam(q, nsteps=12, learning_rate=0.01, return_loss=True)
+    assert torch.allclose(th, td.cpu(), atol=2e-5)
+    assert torch.allclose(lh, ld.cpu(), rtol=1e-4, atol=1e-9)
+
+
+def test_joins_a_device_resident_group():
+    """A linear-link model and a built-in SMF model sharing (shift, sigma) in
+    one OnePointGroup: the device-resident group loop applies."""
+    from multigrad_b200.models import SMFModel, smf
+    from multigrad_b200.ops import group as grp
+    data = smf.make_smf_data(30_000, comm=SELF, device=dev())
+    n = data["log_halo_masses"].numel()
+    lin = LinearLinkBinnedModel(
+        x=data["log_halo_masses"] + 0.1,
+        features=torch.ones(n, 1, device=dev()),
+        bin_edges=np.linspace(9, 10, 8), volume=data["volume"], comm=SELF,
+        device=dev())
+    lin.set_target(lin.calc_sumstats_from_params([-2.0, 0.2]))
+    ref = SMFModel(aux_data=data, comm=SELF, device=dev())
+    group = mg.OnePointGroup(models=(ref, lin), main_comm=SELF)
+    p = torch.tensor([-1.9, 0.3], device=dev())
+    assert group._device_ok(p)
+    lg, gg = group.calc_loss_and_grad_from_params(p.cpu())
+    l1, g1 = ref.calc_loss_and_grad_from_params(p.cpu())
+    l2, g2 = lin.calc_loss_and_grad_from_params(p.cpu())
+    assert torch.allclose(torch.as_tensor(lg).cpu(), (l1 + l2).cpu(),
+                          rtol=1e-5)
+    assert torch.allclose(torch.as_tensor(gg).cpu(), (g1 + g2).cpu(),
+                          rtol=1e-4, atol=1e-7)
+    traj = group.run_adam(p.cpu(), nsteps=150, learning_rate=0.01)
+    assert torch.allclose(traj[-1].cpu(), torch.tensor([-2.0, 0.2]),
+                          atol=0.02), traj[-1]
+
+
 def test_fp8_gate_decision_is_reproducible():
     """The FP8 gate (tools/fp8_gate.py): MXFP8 features are emulated exactly
     on the bf16 kernel; the committed decision (profiles/linlink_fp8_gate.json)

@@ -17,7 +17,8 @@ CASES = CPU_CASES + ["gpu_allreduce_kernels", "gpu_fused_step_uses_one_launch",
                      "gpu_linear_link_world_invariance",
                      "gpu_scatter_nd_over_nvlink", "gpu_group_device_steps",
                      "gpu_bfgs_rank_skew_stress", "gpu_collective_soak",
-                     "gpu_linked_model_world_invariance"]
+                     "gpu_linked_model_world_invariance",
+                     "gpu_linear_link_bfgs_and_group"]
 
 
 def _worlds():
