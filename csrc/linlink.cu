@@ -271,8 +271,13 @@ linlink_selftest_kernel(const __grid_constant__ CUtensorMap wmap,
 // ===========================================================================
 // pipeline depth: the W tile of a stage lives from its TMA until the Jacobian
 // product has consumed it, so the depth has to cover the HBM latency
-__host__ __device__ constexpr int ll_stages(int P) { return P <= 64 ? 8 : 5; }
-constexpr int LL_MAX_STAGES = 8;
+#ifndef LL_STAGES64
+#define LL_STAGES64 8
+#endif
+__host__ __device__ constexpr int ll_stages(int P) {
+  return P <= 64 ? LL_STAGES64 : 5;
+}
+constexpr int LL_MAX_STAGES = 12;
 // independent TMEM accumulators of the Jacobian product: its UMMAs are tiny
 // (64 x P x 16), so a single accumulator chain is bound by the ~95-cycle
 // accumulate latency; K steps are dealt round-robin to LL_NACC chains that
@@ -300,7 +305,7 @@ __host__ __device__ constexpr int ll_nacc(int P) { return P <= 64 ? 4 : 2; }
 #define LL_NCH64 3
 #endif
 #ifndef LL_SETS64
-#define LL_SETS64 4
+#define LL_SETS64 3
 #endif
 #ifndef LL_NCH128
 #define LL_NCH128 3
@@ -322,6 +327,24 @@ __host__ __device__ constexpr int ll_threads(int P) {
   return 32 * (2 + ll_sets(P) * 4 * ll_groups(P));
 }
 constexpr int LL_MAX_CWARPS = 30;
+// The Gaussian operand G of a tile (8 KiB) lives only from the compute phase
+// to the Jacobian product, so it has its own, shorter ring: shared memory goes
+// to W stages instead (the stream is bound by bytes in flight: a stage cycle is
+// HBM latency under load + both products + the compute phase).
+#ifndef LL_GEXTRA64
+#define LL_GEXTRA64 1
+#endif
+#ifndef LL_GEXTRA128
+#define LL_GEXTRA128 0
+#endif
+__host__ __device__ constexpr int ll_gextra(int P) {
+  return P <= 64 ? LL_GEXTRA64 : LL_GEXTRA128;
+}
+__host__ __device__ constexpr int ll_gbufs(int P) {
+  return (ll_sets(P) + ll_gextra(P)) < ll_stages(P)
+             ? ll_sets(P) + ll_gextra(P)
+             : ll_stages(P);
+}
 constexpr float LL_KAPPA = 1.2011224087864498f;
 constexpr float LL_HSCALE = MGB_ERFCX_CSCALE / LL_KAPPA;
 
@@ -333,10 +356,10 @@ constexpr int LL_XSTAGE = 2 * LL_TILE * 4;
 __host__ __device__ inline LinSmemLayout lin_smem_layout(int P) {
   LinSmemLayout L;
   L.w_bytes = (P / LL_FB) * LL_TILE * 128;          // per stage
-  L.th_off = ll_stages(P) * L.w_bytes;
-  L.g_off = L.th_off + (P / LL_FB) * 2048;
-  L.x_off = L.g_off + ll_stages(P) * 8192;
-  L.total = L.x_off + 16384;   // x / weight stages (<= 8 KiB) + spare
+  L.th_off = 0;
+  L.g_off = ll_stages(P) * L.w_bytes;
+  L.x_off = L.g_off + ll_gbufs(P) * 8192;
+  L.total = L.x_off + ll_stages(P) * LL_XSTAGE;
   return L;
 }
 
@@ -350,7 +373,6 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   extern __shared__ __align__(1024) uint8_t smem[];
   const LinSmemLayout L = lin_smem_layout(P);
   uint8_t* s_w = smem;
-  uint8_t* s_th = smem + L.th_off;
   uint8_t* s_g = smem + L.g_off;
   // x (and weights) of a tile travel with its W tile: a 512-byte bulk copy on
   // the same mbarrier.  (Loading them with LDG from the compute warps put a
@@ -360,8 +382,9 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
 
   constexpr int LL_STAGES = ll_stages(P);
   constexpr int NACC = ll_nacc(P);
-  __shared__ uint64_t full_w[LL_MAX_STAGES], mu_full[LL_MAX_STAGES],
-      g_full[LL_MAX_STAGES], empty[LL_MAX_STAGES], d2_done;
+  __shared__ uint64_t full_w[LL_MAX_STAGES],
+      g_full[LL_MAX_STAGES], g_free[LL_MAX_STAGES], empty[LL_MAX_STAGES],
+      d2_done;
   __shared__ uint32_t s_tmem;
   __shared__ float s_cs[LL_MAXE];
   constexpr int LL_THREADS = ll_threads(P);
@@ -402,8 +425,8 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   if (tid == 0) {
     for (int s = 0; s < LL_STAGES; ++s) {
       mbar_init(&full_w[s], 1);
-      mbar_init(&mu_full[s], 1);
       mbar_init(&g_full[s], CWS);
+      mbar_init(&g_free[s], 1);
       mbar_init(&empty[s], 1);
     }
     mbar_init(&d2_done, 1);
@@ -417,13 +440,15 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
   }
   if (tid < E)
     s_cs[tid] = (float)(((double)md.edges[tid] - (double)x0) * ks_d);
-  write_theta_tile(s_th, pv, P, md.nfeat, tid, LL_THREADS);   // theta planes (B of #1)
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const uint32_t tm_d2 = tmem + 128;    // P columns; D1 stage s at column 16*s
+  constexpr int NGB = ll_gbufs(P);
+  // (the parity waits of the compute warps rely on both)
+  static_assert(NGB >= SETS && NGB <= LL_STAGES, "G ring length");
+  const uint32_t tm_d2 = tmem;          // the D2 accumulators
 
   int fail = 0;
   if (warp == 0) {
@@ -459,7 +484,6 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
     // uniform-datapath instructions per UMMA, which made this single thread
     // the bottleneck of the kernel (~95 cycles per 32-cycle UMMA).
     {
-      const uint32_t id1 = idesc_bf16_f32(128, 16, false, false);
       // M = 64: only 32 rows of G are meaningful; the 64-row form halves the
       // operand fetch.  Its accumulator rows r land in TMEM lane
       // 32*(r/16) + r%16 (probed with tools/probe_m64.py).
@@ -474,46 +498,21 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
 #endif
       const uint64_t dk = smem_desc_sw128(0, 16, 1024);                // K-major
       const uint64_t dmn = smem_desc_sw128(0, LL_TILE * 128, 1024);    // MN-major
-      const uint64_t th0 = dk + (smem_u32(s_th) >> 4);
-      // Two event streams: forward products are issued as soon as a W tile
-      // lands (up to LL_STAGES tiles ahead), Jacobian products as soon as the
-      // compute warps have published G for a tile.
-      long long n1 = 0, n2 = 0;
+      // Jacobian products are issued as soon as the compute warps have
+      // published G for a tile.
+      long long n2 = 0;
       unsigned long long t_idle = 0;
       while (n2 < my_tiles) {
         bool progressed = false;
-        if (n1 < my_tiles) {
-          const int s = (int)(n1 % LL_STAGES);
-          const uint32_t ph = (uint32_t)((n1 / LL_STAGES) & 1);
-          if (mbar_test_wait(&full_w[s], ph)) {
-            LL_TR(1, n1);
-            tc_fence_after();
-            if (elect_one()) {
-              const uint64_t a0 = dk + (smem_u32(s_w + s * L.w_bytes) >> 4);
-              const uint32_t d1 = tmem + s * 16;
-#pragma unroll
-              for (int kstep = 0; kstep < ((LL_ABL & 8) ? 0 : P / 16); ++kstep) {
-                const int fb = kstep >> 2, kk = kstep & 3;
-                umma_bf16(d1, a0 + (fb * (LL_TILE * 128 / 16) + kk * 2),
-                          th0 + (fb * (2048 / 16) + kk * 2), id1, kstep > 0);
-              }
-              umma_commit(&mu_full[s]);
-              LL_TR(6, n1);
-            }
-            __syncwarp();
-            ++n1;
-            progressed = true;
-          }
-        }
-        if (n2 < n1) {
+        {
           const int s = (int)(n2 % LL_STAGES);
-          const uint32_t ph = (uint32_t)((n2 / LL_STAGES) & 1);
-          if (mbar_test_wait(&g_full[s], ph)) {
+          const int gb = (int)(n2 % NGB);
+          if (mbar_test_wait(&g_full[gb], (uint32_t)((n2 / NGB) & 1))) {
             LL_TR(4, n2);
             tc_fence_after();
             if (elect_one()) {
               const uint64_t b0 = dmn + (smem_u32(s_w + s * L.w_bytes) >> 4);
-              const uint64_t a0 = dk + (smem_u32(s_g + s * 8192) >> 4);
+              const uint64_t a0 = dk + (smem_u32(s_g + gb * 8192) >> 4);
               const bool first = n2 == 0;
 #pragma unroll
               for (int kstep = 0; kstep < ((LL_ABL & 1) ? 0 : LL_TILE / 16);
@@ -531,6 +530,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
 #endif
               }
               umma_commit(&empty[s]);
+              umma_commit(&g_free[gb]);
               LL_TR(7, n2);
             }
             __syncwarp();
@@ -585,6 +585,45 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       goff[e] = sw128_offset_16b(odd ? 16u + (r ^ 4u) : r, ko & ~1u) +
                 (uint32_t)(o >> 6) * 4096u;
     }
+    // Forward product mu = W . theta of this warp's 32 objects on the
+    // warp-level tensor path: ldmatrix of the SW128 tile + mma.sync
+    // m16n8k16 (bf16 x bf16 -> fp32) against a register-resident B fragment
+    // whose columns 0..2 are three bf16 planes of theta (fp32-grade product).
+    // A tcgen05 product for it (M128 N16) re-read the whole 16 KiB tile through
+    // the UMMA operand path, which -- not HBM -- then bounded the kernel
+    // (measured: ~45 B/clk of operand fetch per SM for these tiny-N shapes).
+    uint32_t bfr[P / 16][2];
+    {
+      const int pl = lane >> 2, q = lane & 3;      // plane (column), k pair
+#pragma unroll
+      for (int kk = 0; kk < P / 16; ++kk) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t word = 0;
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            const int f = kk * 16 + h * 8 + 2 * q + i;
+            float th = (pl < 3 && f < md.nfeat) ? pv[f] : 0.0f;
+            const float p0 = bf16_val(th);
+            const float p1 = bf16_val(th - p0);
+            const float vv = pl == 0 ? p0 : pl == 1 ? p1 : (th - p0) - p1;
+            word |= (uint32_t)bf16_bits(vv) << (16 * i);
+          }
+          bfr[kk][h] = word;
+        }
+      }
+    }
+    // ldmatrix row address of this lane: matrix lane>>3 = (row half, k half),
+    // row lane&7; the two 16-object blocks are 2 KiB apart
+    uint32_t aoff[4];
+    {
+      const int mi = lane >> 3;
+      const uint32_t R = (uint32_t)(quad * 32 + (mi & 1) * 8 + (lane & 7));
+#pragma unroll
+      for (int kc = 0; kc < 4; ++kc)
+        aoff[kc] = R * 128u + (((uint32_t)(2 * kc + (mi >> 1)) ^ (R & 7u)) << 4);
+    }
+    const int src_lane = 4 * (lane & 7) + ((lane >> 3) & 1);
     long long obj = (tile0 + (long long)set * tstride) * LL_TILE + o;
     for (long long it = set; it < my_tiles; it += SETS) {
       const int s = (int)(it % LL_STAGES);
@@ -592,8 +631,23 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       const bool valid = obj < md.n;
       const bool whole = obj - o + LL_TILE <= md.n;     // warp-uniform
       if (grp == 0 && quad == 0 && lane == 0) LL_TR(5, it);
-      // the tile's own barrier first: it is what makes the bulk-copied x
-      // visible to this thread (long complete by the time mu is there)
+      // Parity waits are only safe on a barrier that is at most one phase
+      // behind or ahead.  TMA completions are not ordered between tiles and a
+      // set skips the tiles of the other sets, so on its own this warp could
+      // reach stage s while the PREVIOUS tile of that stage (it - LL_STAGES,
+      // another set's) has not landed yet -- the parity test would then pass
+      // on the phase before that (seen as wrong sums, barrier time-outs and
+      // launch failures at P = 128).  The G buffer wait closes that: Jacobian
+      // products are issued in tile order, so "product it - NGB complete"
+      // implies every tile up to it - NGB >= it - LL_STAGES has landed; the
+      // g_free parity itself is safe because NGB >= SETS.
+      const int gb = (int)(it % NGB);
+      if (it >= NGB &&
+          !mbar_wait(&g_free[gb], (uint32_t)(((it / NGB) + 1) & 1))) {
+        fail = 1;
+        break;
+      }
+      // the tile's own barrier: it also makes the bulk-copied x visible
       if (!mbar_wait(&full_w[s], ph)) { fail = 1; break; }
       float xv = 1.0e30f, wv = 0.0f;
       if (!(LL_ABL & 16)) {
@@ -606,29 +660,64 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
         }
       }
       obj += (long long)SETS * tstride * LL_TILE;
-      if (!mbar_wait(&mu_full[s], ph)) { fail = 1; break; }
       if (grp == 0 && quad == 0 && lane == 0) LL_TR(2, it);
       if (lane == 0) LL_TRW(cw, 0, it);
-      tc_fence_after();
-      uint32_t v[4];
-      if (LL_ABL & 32) {
+      float muf = 0.0f;
+      // lanes leave the polling loop of the barrier wait one by one; the
+      // .aligned warp-level instructions below need them back together
+      __syncwarp();
+      if (!(LL_ABL & 32)) {
+        const uint32_t wbase = smem_u32(s_w + s * L.w_bytes);
+        float d[2][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) v[i] = 0u;
-      } else {
-        tmem_ld_x4(tmem + s * 16 + ((uint32_t)(quad * 32) << 16), v);
-        tmem_ld_wait();
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) d[b][i] = 0.0f;
+#pragma unroll
+        for (int kk = 0; kk < P / 16; ++kk) {
+#pragma unroll
+          for (int b = 0; b < 2; ++b) {
+            uint32_t a0, a1, a2, a3;
+            const uint32_t addr = wbase + aoff[kk & 3] +
+                                  (uint32_t)((kk >> 2) * (LL_TILE * 128) +
+                                             b * 2048);
+            asm volatile(
+                "ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                : "r"(addr));
+            asm volatile(
+                "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 "
+                "{%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                : "+f"(d[b][0]), "+f"(d[b][1]), "+f"(d[b][2]), "+f"(d[b][3])
+                : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(bfr[kk][0]),
+                  "r"(bfr[kk][1]));
+          }
+        }
+        // d[b][0..1]: row g = lane>>2 of block b, columns 2q, 2q+1;
+        // d[b][2..3]: row g + 8.  Columns 0..2 are the planes: lanes q = 0, 1
+        // hold them, their sum is mu of the row.
+        float v00 = d[0][0] + d[0][1], v01 = d[0][2] + d[0][3];
+        float v10 = d[1][0] + d[1][1], v11 = d[1][2] + d[1][3];
+        v00 += __shfl_xor_sync(0xffffffffu, v00, 1);
+        v01 += __shfl_xor_sync(0xffffffffu, v01, 1);
+        v10 += __shfl_xor_sync(0xffffffffu, v10, 1);
+        v11 += __shfl_xor_sync(0xffffffffu, v11, 1);
+        // object o = 16 b + 8 half + g is served by lane 4 g + half, which
+        // offers (b = 0, its half) and (b = 1, its half)
+        const bool hsel = lane & 1;
+        const float m0 = __shfl_sync(0xffffffffu, hsel ? v01 : v00, src_lane);
+        const float m1 = __shfl_sync(0xffffffffu, hsel ? v11 : v10, src_lane);
+        muf = (lane & 16) ? m1 : m0;
       }
-      const float muf = (__uint_as_float(v[0]) + __uint_as_float(v[1])) +
-                        __uint_as_float(v[2]);
       // u = (x - x0) + W.theta ; zs_e = cs_e - ks*u
       const float u = valid ? (xv - x0) + muf : 1.0e30f;
-      uint8_t* gs = s_g + s * 8192;
+      uint8_t* gs = s_g + gb * 8192;
       if (LL_ABL & 4) {            // no math, no G stores: hand the tile on
         accT[0] += u;
         if (!(LL_ABL & 64)) fence_proxy_async_smem();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&g_full[s]);
+        if (lane == 0) mbar_arrive(&g_full[gb]);
         continue;
       }
 #pragma unroll
@@ -692,7 +781,7 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&g_full[s]);
+      if (lane == 0) mbar_arrive(&g_full[gb]);
       if (grp == 0 && quad == 0 && lane == 0) LL_TR(3, it);
       if (lane == 0) LL_TRW(cw, 1, it);
     }
