@@ -147,8 +147,22 @@ __device__ __forceinline__ void eb_st_release_gpu_s32(int* p, int v) {
 // Per-edge accumulators are scalar: a packed FADD2 and two FADDs cost the
 // same FMA-pipe time and four registers per edge are what lets ptxas keep the
 // edges' Horner chains in flight together.
+// EB_ACC2 (off): T, G, Z accumulate the two objects of a pair separately
+// (packed FFMA2 / FADD2 instead of two scalar FFMA / FADD each), the halves
+// added once at the end.  Measured SLOWER (714 vs 663 us per step at 1e8
+// objects with 12 warps, 748 with 8): a packed instruction holds the issue
+// port for two cycles, so it saves nothing over two scalar ones, and the 33
+// extra registers cost scheduling freedom.
+#ifndef EB_ACC2
+#define EB_ACC2 0
+#endif
 struct EdgeAcc {
+#if EB_ACC2
+  float2 T, G, Z;
+  float O;
+#else
   float T, O, G, Z;
+#endif
 };
 
 // Gaussian recurrence (uniform edges).  With A0 = ET/2 the central edge of a
@@ -323,8 +337,12 @@ __device__ __forceinline__ void eb_stage_b(EdgeAcc* __restrict__ a, int i0,
           __float_as_uint(g[j].x) | (~__float_as_uint(zs[j].x) & 0x80000000u));
       const float gy = __uint_as_float(
           __float_as_uint(g[j].y) | (~__float_as_uint(zs[j].y) & 0x80000000u));
+#if EB_ACC2
+      ac.T = vfma(p[j], f2(gx, gy), ac.T);
+#else
       ac.T = fmaf(p[j].x, gx, ac.T);
       ac.T = fmaf(p[j].y, gy, ac.T);
+#endif
     }
   }
 #pragma unroll
@@ -348,10 +366,15 @@ __device__ __forceinline__ void eb_stage_b(EdgeAcc* __restrict__ a, int i0,
   for (int j = 0; j < CH; ++j) {
     if (i0 + j < ET) {
       EdgeAcc& ac = a[OD::edge(i0 + j)];
+#if EB_ACC2
+      ac.G = vadd(ac.G, g[j]);
+      ac.Z = vfma(zs[j], g[j], ac.Z);
+#else
       ac.G += g[j].x;
       ac.G += g[j].y;
       ac.Z = fmaf(zs[j].x, g[j].x, ac.Z);
       ac.Z = fmaf(zs[j].y, g[j].y, ac.Z);
+#endif
     }
   }
 }
@@ -581,8 +604,12 @@ __device__ __forceinline__ void accumulate_group(
   EdgeAcc acc[ET];
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
-    acc[e].T = 0.f; acc[e].O = 0.f;
-    acc[e].G = 0.f; acc[e].Z = 0.f;
+#if EB_ACC2
+    acc[e].T = f2s(0.f); acc[e].G = f2s(0.f); acc[e].Z = f2s(0.f);
+#else
+    acc[e].T = 0.f; acc[e].G = 0.f; acc[e].Z = 0.f;
+#endif
+    acc[e].O = 0.f;
   }
   // next tile after `t` (or -1): static stride first, then claims of two
   // consecutive tiles from the group's counter (warp-uniform)
@@ -685,15 +712,24 @@ __device__ __forceinline__ void accumulate_group(
   }
 #pragma unroll
   for (int e = 0; e < ET; ++e) {
+#if EB_ACC2
+    const float t = mgb_warp_sum(acc[e].T.x + acc[e].T.y);
+#else
     const float t = mgb_warp_sum(acc[e].T);
+#endif
     // unweighted O counts objects with z < 0: Phi = (N - O) + T, and N drops
     // out of every difference between edges
     const double o =
         WEIGHTED ? (double)mgb_warp_sum(acc[e].O)
                  : -(double)__reduce_add_sync(0xffffffffu,
                                               __float_as_int(acc[e].O));
+#if EB_ACC2
+    const float g = mgb_warp_sum(acc[e].G.x + acc[e].G.y);
+    const float z = mgb_warp_sum(acc[e].Z.x + acc[e].Z.y);
+#else
     const float g = mgb_warp_sum(acc[e].G);
     const float z = mgb_warp_sum(acc[e].Z);
+#endif
     if (lane == 0) {
       s_out[4 * e + 0] = (double)t;
       s_out[4 * e + 1] = o;
