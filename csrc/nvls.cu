@@ -20,6 +20,7 @@
 // Reference counterpart: none -- the reference reduces on the host through
 // MPI (multigrad/multigrad.py:149-183).
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 #include "mgb_common.cuh"
 
@@ -255,6 +256,10 @@ namespace {
 
 #define NV_BLOCK 512
 #define NV_MAX_CTAS 296
+#ifndef NV_UNROLL
+#define NV_UNROLL 8
+#endif
+#define NV_RESIDENT_CTAS 16
 
 __device__ __forceinline__ float4 mc_ld_reduce_f4(const float4* p) {
   float4 v;
@@ -367,15 +372,20 @@ nvls_allreduce_f32_kernel(const MgbPeerTable pt, float4* __restrict__ uc,
     const long long sub = (len + W - 1) / W;
     const long long slo = lo + sub * me;
     const long long shi = min(slo + sub, hi);
-    long long i = slo + tid;
-    for (; i + 3 * NV_BLOCK < shi; i += 4 * NV_BLOCK) {
-      float4 v[4];
+    // NV_UNROLL independent in-switch reductions in flight per thread, the
+    // ragged end predicated instead of falling back to one at a time (a
+    // 64 MiB message leaves each CTA and rank ~1800 float4s: less than one
+    // full unrolled pass, so the old remainder loop did all the work with a
+    // single outstanding request per thread)
+    for (long long i = slo + tid; i < shi; i += (long long)NV_UNROLL * NV_BLOCK) {
+      float4 v[NV_UNROLL];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = mc_ld_reduce_f4(mc + i + k * NV_BLOCK);
+      for (int k = 0; k < NV_UNROLL; ++k)
+        if (i + k * NV_BLOCK < shi) v[k] = mc_ld_reduce_f4(mc + i + k * NV_BLOCK);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) mc_st_f4(mc + i + k * NV_BLOCK, v[k]);
+      for (int k = 0; k < NV_UNROLL; ++k)
+        if (i + k * NV_BLOCK < shi) mc_st_f4(mc + i + k * NV_BLOCK, v[k]);
     }
-    for (; i < shi; i += NV_BLOCK) mc_st_f4(mc + i, mc_ld_reduce_f4(mc + i));
     if (INPLACE && blockIdx.x == 0 && me == 0 && tid < ntail) {
       float* p = reinterpret_cast<float*>(mc) + tail_start + tid;
       mc_st_f1(p, mc_ld_reduce_f1(p));
@@ -442,6 +452,14 @@ extern "C" int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc,
   // CTAs per SM are resident, every CTA waits for its peers)
   long long ctas = (n4t + 4 * NV_BLOCK - 1) / (4 * NV_BLOCK);
   if (ctas > NV_MAX_CTAS) ctas = NV_MAX_CTAS;
+  // Resident tensors have no copy phases; their in-switch phase runs best
+  // from few CTAs with many requests in flight each (8 GPUs, 64 MiB: 171 us
+  // with 16 CTAs, 185 with 64, 203 with 296; tools/nvls_tune.py)
+  if (inplace && ctas > NV_RESIDENT_CTAS) ctas = NV_RESIDENT_CTAS;
+  if (const char* e = getenv("MULTIGRAD_B200_NVLS_CTAS")) {   // tuning aid
+    const long long c = atoll(e);
+    if (c >= 1 && c <= NV_MAX_CTAS && c < ctas) ctas = c;
+  }
   if (ctas < 1) ctas = 1;
   if (inplace) {
     float4* mcd = (float4*)((char*)mc + (d0 - u0));
