@@ -133,6 +133,121 @@ __device__ __forceinline__ unsigned mgb_ll_wait(const MgbPeerTable& pt,
 // they do only after having consumed e).
 // `sh` in: local values, out: totals.  `stage` is scratch of world*m doubles
 // in shared memory.  Requires 2*m <= pt.ll_units.
+// Fetch doubles that peers pushed into my slots (two tagged words per double,
+// from unit `unit0` on).  Item i of count * nsrc is (si = i / count, j = i %
+// count): source rank src_of(si), double j, stored to *out_of(si, j) unless
+// that returns nullptr.  Four items (eight slot loads) are in flight per
+// thread before any tag is looked at.
+template <typename SrcOf, typename OutOf>
+__device__ __forceinline__ void mgb_ll_gather(const MgbPeerTable& pt,
+                                              unsigned parity, unsigned epoch,
+                                              unsigned unit0, int count,
+                                              int nsrc, SrcOf src_of,
+                                              OutOf out_of) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  for (int i0 = tid; i0 < count * nsrc; i0 += 4 * nt) {
+    unsigned long long lo[4], hi[4];
+    double* dstp[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = i0 + k * nt;
+      lo[k] = hi[k] = 0ull;
+      dstp[k] = nullptr;
+      if (i < count * nsrc) {
+        const int si = i / count, j = i - si * count;
+        dstp[k] = out_of(si, j);
+        if (dstp[k]) {
+          const int s = src_of(si);
+          lo[k] = mgb_ld_sys_u64(
+              mgb_ll_slot(pt, pt.rank, parity, s, unit0 + 2u * j));
+          hi[k] = mgb_ld_sys_u64(
+              mgb_ll_slot(pt, pt.rank, parity, s, unit0 + 2u * j + 1u));
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (dstp[k]) {
+        const int i = i0 + k * nt;
+        const int si = i / count, j = i - si * count;
+        const int s = src_of(si);
+        unsigned l = (unsigned)lo[k], h = (unsigned)hi[k];
+        if ((unsigned)(lo[k] >> 32) != epoch)
+          l = mgb_ll_wait(
+              pt, mgb_ll_slot(pt, pt.rank, parity, s, unit0 + 2u * j), epoch);
+        if ((unsigned)(hi[k] >> 32) != epoch)
+          h = mgb_ll_wait(
+              pt, mgb_ll_slot(pt, pt.rank, parity, s, unit0 + 2u * j + 1u),
+              epoch);
+        *dstp[k] = __hiloint2double((int)h, (int)l);
+      }
+    }
+  }
+}
+
+// Long vectors (a K x P Jacobian: m ~ 1300) go in two rounds -- every rank
+// reduces one slice of m / W doubles (in rank order, so the totals stay
+// bit-identical everywhere and equal to the one-round result) and sends the
+// sums to everybody: 2 m (W-1)/W doubles leave a rank instead of m (W-1).
+// All of them come from the one CTA that runs the exchange, and the remote
+// stores one SM can keep in flight bound it: 8 GPUs, m = 1300 cost 114 us in
+// one round.  Short vectors keep the single round (one latency less).
+#ifndef MGB_LL_TWO_ROUND_MIN
+#define MGB_LL_TWO_ROUND_MIN 192
+#endif
+__device__ __forceinline__ void mgb_ll_allreduce_two_round(
+    const MgbPeerTable& pt, double* sh, double* stage, int m, unsigned parity,
+    unsigned epoch) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int W = pt.world, me = pt.rank;
+  const int c = (m + W - 1) / W;            // slice length
+  const unsigned* words = reinterpret_cast<const unsigned*>(sh);
+  // round 1: my contribution to slice d goes to rank d (units [0, 2c))
+  for (int i = tid; i < 2 * c * (W - 1); i += nt) {
+    const int pi = i / (2 * c), u = i - pi * (2 * c);
+    int dst = me + 1 + pi;
+    if (dst >= W) dst -= W;
+    const int j = dst * c + (u >> 1);
+    if (j < m)
+      mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, me, (unsigned)u),
+                     ((unsigned long long)epoch << 32) | words[2 * j + (u & 1)]);
+  }
+  const int lo_j = me * c;
+  const int mine = lo_j < m ? (lo_j + c <= m ? c : m - lo_j) : 0;
+  // stage[si * mine + j]: contribution of the si-th other rank to my slice
+  if (mine > 0)
+    mgb_ll_gather(pt, parity, epoch, 0u, mine, W - 1,
+                  [&](int si) { return si < me ? si : si + 1; },
+                  [&](int si, int j) { return stage + si * mine + j; });
+  __syncthreads();
+  double* red = stage + (size_t)(W - 1) * c;        // my reduced slice
+  for (int j = tid; j < mine; j += nt) {
+    double acc = 0.0;
+    for (int s = 0; s < W; ++s)
+      acc += s == me ? sh[lo_j + j] : stage[(s < me ? s : s - 1) * mine + j];
+    red[j] = acc;
+  }
+  __syncthreads();
+  // round 2: the sums of my slice go to everybody (units [2c, 4c))
+  const unsigned* rw = reinterpret_cast<const unsigned*>(red);
+  for (int i = tid; i < 2 * mine * (W - 1); i += nt) {
+    const int pi = i / (2 * mine), u = i - pi * (2 * mine);
+    int dst = me + 1 + pi;
+    if (dst >= W) dst -= W;
+    mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, me, (unsigned)(2 * c + u)),
+                   ((unsigned long long)epoch << 32) | rw[u]);
+  }
+  for (int j = tid; j < mine; j += nt) sh[lo_j + j] = red[j];
+  // the other slices, straight into sh (slice s ends at m)
+  mgb_ll_gather(pt, parity, epoch, (unsigned)(2 * c), c, W - 1,
+                [&](int si) { return si < me ? si : si + 1; },
+                [&](int si, int j) -> double* {
+                  const int g = (si < me ? si : si + 1) * c + j;
+                  return g < m ? sh + g : nullptr;
+                });
+  __syncthreads();
+}
+
 __device__ __forceinline__ void mgb_ll_allreduce_f64(const MgbPeerTable& pt,
                                                      double* sh, double* stage,
                                                      int m) {
@@ -146,6 +261,11 @@ __device__ __forceinline__ void mgb_ll_allreduce_f64(const MgbPeerTable& pt,
   const unsigned parity = epoch & 1u;
   const int units = 2 * m;
   const int W = pt.world;
+  if (m >= MGB_LL_TWO_ROUND_MIN && W > 2) {
+    mgb_ll_allreduce_two_round(pt, sh, stage, m, parity, epoch);
+    if (tid == 0) mgb_st_sys_u32(ctrl + MGB_CTRL_EPOCH, epoch);
+    return;
+  }
   const unsigned* words = reinterpret_cast<const unsigned*>(sh);
   // push to the W-1 peers, staggered so that not everyone hits rank 0 first
   for (int i = tid; i < units * (W - 1); i += nt) {
@@ -155,21 +275,13 @@ __device__ __forceinline__ void mgb_ll_allreduce_f64(const MgbPeerTable& pt,
     mgb_st_sys_u64(mgb_ll_slot(pt, dst, parity, pt.rank, (unsigned)u),
                    ((unsigned long long)epoch << 32) | words[u]);
   }
-  // gather: thread (s, j) fetches double j of source s into stage[s*m+j]
-  for (int i = tid; i < m * W; i += nt) {
-    const int s = i / m, j = i - s * m;
-    double val;
-    if (s == pt.rank) {
-      val = sh[j];
-    } else {
-      unsigned lo = mgb_ll_wait(
-          pt, mgb_ll_slot(pt, pt.rank, parity, s, 2u * j), epoch);
-      unsigned hi = mgb_ll_wait(
-          pt, mgb_ll_slot(pt, pt.rank, parity, s, 2u * j + 1u), epoch);
-      val = __hiloint2double((int)hi, (int)lo);
-    }
-    stage[i] = val;
-  }
+  // gather: double j of source s into stage[s*m+j] (own values copied)
+  for (int j = tid; j < m; j += nt) stage[pt.rank * m + j] = sh[j];
+  mgb_ll_gather(pt, parity, epoch, 0u, m, W - 1,
+                [&](int si) { return si < pt.rank ? si : si + 1; },
+                [&](int si, int j) {
+                  return stage + (si < pt.rank ? si : si + 1) * m + j;
+                });
   __syncthreads();
   for (int j = tid; j < m; j += nt) {
     double acc = 0.0;
