@@ -29,6 +29,10 @@ def main():
     ap.add_argument("--num-features", type=int, default=4)
     ap.add_argument("--num-steps", type=int, default=400)
     ap.add_argument("--learning-rate", type=float, default=0.01)
+    ap.add_argument("--weighted", action="store_true",
+                    help="give every object a weight (e.g. completeness)")
+    ap.add_argument("--polish", action="store_true",
+                    help="finish with L-BFGS-B (replicated on every rank)")
     args = ap.parse_args()
     comm, dev = mg.COMM, mg.parallel.local_device()
     n = args.num_halos // comm.size
@@ -39,9 +43,11 @@ def main():
                       0.3 * torch.randn(n, F - 1, generator=g)], dim=1)
     truth = torch.cat([torch.tensor([-2.0]), 0.1 * torch.ones(F - 1),
                        torch.tensor([0.2])])          # theta..., sigma
+    w = (0.5 + torch.rand(n, generator=g)).to(dev) if args.weighted else None
     model = LinearLinkBinnedModel(
         x=x.to(dev), features=feat.to(dev), bin_edges=np.linspace(9, 10, 11),
-        volume=10.0 * args.num_halos, target_sumstats=np.ones(10))
+        volume=10.0 * args.num_halos, target_sumstats=np.ones(10), weights=w,
+        loss_eps=1e-10)
     model.set_target(model.calc_sumstats_from_params(truth))
     guess = truth + torch.cat([torch.tensor([0.2]),
                                -0.1 * torch.ones(F - 1),
@@ -54,6 +60,12 @@ def main():
               f"{float(losses[0]):.4f} -> {float(losses[-1]):.2e}")
         print("truth :", [round(float(v), 4) for v in truth])
         print("fitted:", [round(float(v), 4) for v in traj[-1].cpu()])
+    if args.polish:
+        res = model.run_bfgs(traj[-1].cpu(), maxsteps=50,
+                             param_bounds=[(None, None)] * F + [(0.02, 2.0)])
+        if comm.rank == 0:
+            print(f"L-BFGS-B: loss {res.fun:.3e} after {res.nfev} evaluations")
+            print("polished:", [round(float(v), 4) for v in res.x])
     mg.shutdown()
 
 
