@@ -66,9 +66,6 @@ constexpr int LL_GROWS = 32;     // rows of G: 16 x g_hi, 16 x g_lo
 #ifndef LL_SWAP
 #define LL_SWAP 1
 #endif
-#ifndef LL_IDLE_SLEEP_NS
-#define LL_IDLE_SLEEP_NS 0
-#endif
 #ifndef LL_ABL
 #define LL_ABL 0   // ablation bits for tuning experiments (0 in production)
 #endif
@@ -500,55 +497,45 @@ linlink_step_kernel(const __grid_constant__ CUtensorMap wmap,
       const uint64_t dmn = smem_desc_sw128(0, LL_TILE * 128, 1024);    // MN-major
       // Jacobian products are issued as soon as the compute warps have
       // published G for a tile.
-      long long n2 = 0;
-      unsigned long long t_idle = 0;
-      while (n2 < my_tiles) {
-        bool progressed = false;
-        {
-          const int s = (int)(n2 % LL_STAGES);
-          const int gb = (int)(n2 % NGB);
-          if (mbar_test_wait(&g_full[gb], (uint32_t)((n2 / NGB) & 1))) {
-            LL_TR(4, n2);
-            tc_fence_after();
-            if (elect_one()) {
-              const uint64_t b0 = dmn + (smem_u32(s_w + s * L.w_bytes) >> 4);
-              const uint64_t a0 = dk + (smem_u32(s_g + gb * 8192) >> 4);
-              const bool first = n2 == 0;
+      // One event stream (G published, in tile order), so the warp blocks in
+      // mbarrier.try_wait instead of spinning over test_wait: a spinning
+      // issuer takes issue slots from the three compute warps of its SM
+      // sub-partition, and the slowest of a tile's four warps sets the time
+      // its stage stays occupied (tools/linlink_trace.py: the quadrant-1
+      // warps finished 0.2-0.75 us after the others).
+      for (long long n2 = 0; n2 < my_tiles; ++n2) {
+        const int s = (int)(n2 % LL_STAGES);
+        const int gb = (int)(n2 % NGB);
+        if (!mbar_wait(&g_full[gb], (uint32_t)((n2 / NGB) & 1))) {
+          fail = 1;   // bounded: a broken pipeline must not hang the GPU
+          break;
+        }
+        __syncwarp();
+        LL_TR(4, n2);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t b0 = dmn + (smem_u32(s_w + s * L.w_bytes) >> 4);
+          const uint64_t a0 = dk + (smem_u32(s_g + gb * 8192) >> 4);
+          const bool first = n2 == 0;
 #pragma unroll
-              for (int kstep = 0; kstep < ((LL_ABL & 1) ? 0 : LL_TILE / 16);
-                   ++kstep) {
+          for (int kstep = 0; kstep < ((LL_ABL & 1) ? 0 : LL_TILE / 16);
+               ++kstep) {
 #if LL_SWAP
-                umma_bf16(tm_d2 + (kstep % NACC) * LL_GROWS,
-                          b0 + kstep * (2048 / 16),
-                          a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
-                          id2, !first || kstep >= NACC);
+            umma_bf16(tm_d2 + (kstep % NACC) * LL_GROWS,
+                      b0 + kstep * (2048 / 16),
+                      a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2), id2,
+                      !first || kstep >= NACC);
 #else
-                umma_bf16(tm_d2 + (kstep % NACC) * P,
-                          a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
-                          b0 + kstep * (2048 / 16), id2,
-                          !first || kstep >= NACC);
+            umma_bf16(tm_d2 + (kstep % NACC) * P,
+                      a0 + ((kstep >> 2) * (4096 / 16) + (kstep & 3) * 2),
+                      b0 + kstep * (2048 / 16), id2, !first || kstep >= NACC);
 #endif
-              }
-              umma_commit(&empty[s]);
-              umma_commit(&g_free[gb]);
-              LL_TR(7, n2);
-            }
-            __syncwarp();
-            ++n2;
-            progressed = true;
           }
+          umma_commit(&empty[s]);
+          umma_commit(&g_free[gb]);
+          LL_TR(7, n2);
         }
-        if (progressed) {
-          t_idle = 0;
-        } else {   // bounded: a broken pipeline must not hang the GPU
-          unsigned long long now;
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-          if (t_idle == 0) t_idle = now;
-          else if (now - t_idle > 2000000000ull) { fail = 1; break; }
-          // do not steal issue slots from the compute warps that share this
-          // SM sub-partition while there is nothing to issue
-          if (LL_IDLE_SLEEP_NS > 0) __nanosleep(LL_IDLE_SLEEP_NS);
-        }
+        __syncwarp();
       }
       // Only when somebody will wait for it: a commit is an *asynchronous*
       // arrive, and a CTA without tiles would exit before it lands -- the

@@ -8,9 +8,11 @@ Builds the traced variant if it is missing, runs a few steps, then reads the
 SM-clock stamps CTA 0 recorded for 256 consecutive tiles and prints where a
 tile spends its time between the TMA issue and the release of its stage:
 
-    0 TMA issued -> 1 W landed (issuer saw full_w) -> UMMA#1 -> 2 compute warp
-    passed mu_full (5 = when it started waiting) -> 3 G published -> 4 issuer
-    saw g_full -> UMMA#2 -> stage free (= event 0 of tile + stages)
+    0 TMA issued (W, x, weights) -> 2 the tile's compute warps passed full_w
+    (5 = when they started waiting: G buffer first, then the tile) -> forward
+    product (ldmatrix + mma.sync), erfc math, G stores -> 3 G published ->
+    4 issuer saw g_full -> Jacobian UMMAs -> 7 committed -> stage free (= event
+    0 of tile + stages)
 """
 import argparse
 import ctypes as C
@@ -86,34 +88,35 @@ def main():
     period = np.diff(t[0])[ok]
     print(f"tiles traced: {NT}, stages {stages}; tile period "
           f"{period.mean() / ghz / 1e3:.3f} us")
-    stat("0->1 TMA issue -> W landed (issuer)", t[1] - t[0])
-    stat("1->2 UMMA#1 -> compute warp passes mu_full", t[2] - t[1])
-    stat("5->2 compute warp waiting for mu_full", t[2] - t[5])
-    stat("2->3 compute (tcgen05.ld, math, G stores)", t[3] - t[2])
+    stat("0->2 TMA issue -> compute warps have the tile", t[2] - t[0])
+    stat("5->2 compute warps waiting (G buffer + tile)", t[2] - t[5])
+    stat("2->3 forward product, math, G stores", t[3] - t[2])
     stat("3->4 G published -> issuer sees g_full", t[4] - t[3])
-    stat("1->6 issuer: UMMA#1 issue + commit", t[6] - t[1])
-    stat("4->7 issuer: UMMA#2 issue + commit", t[7] - t[4])
+    stat("4->7 issuer: Jacobian UMMAs issue + commit", t[7] - t[4])
     rel = np.roll(t[0], -stages)
-    stat("4->0' UMMA#2 -> stage free -> next TMA issue", rel - t[4])
+    stat("4->0' Jacobian product -> stage free -> next TMA", rel - t[4])
     stat("0->0' stage residency", rel - t[0])
-    # per compute warp: when it passed mu_full and when it published G,
+    # per compute warp: when it had its tile and when it published G,
     # relative to the earliest warp of the same tile
-    wb = (C.c_longlong * (24 * 2 * NT))()
+    sets = int(os.environ.get("LL_TRACE_SETS", "3"))
+    wb = (C.c_longlong * (32 * 2 * NT))()
     assert lib.mgb_linlink_trace_read_warps(wb) == 0
-    w = np.frombuffer(wb, dtype=np.int64).reshape(24, 2, NT).astype(np.float64)
-    print("compute warp: set grp quad | busy us | start lag us | finish lag us")
-    for st in range(2):
-        idx = np.arange(8 + (st - 8) % 2, NT - stages, 2)     # tiles of this set
-        ws = w[st * 12:(st + 1) * 12][:, :, idx]
+    w = np.frombuffer(wb, dtype=np.int64).reshape(32, 2, NT).astype(np.float64)
+    print("compute warp: set quad | busy us | start lag us | finish lag us")
+    t0 = 300                                   # LL_TRACE_T0 in csrc/linlink.cu
+    for st in range(sets):
+        first = 8 + (st - (t0 + 8)) % sets     # first traced tile of this set
+        idx = np.arange(first, NT - stages, sets)
+        ws = w[st * 4:(st + 1) * 4][:, :, idx]
         first_start = ws[:, 0].min(0)
         first_done = ws[:, 1].min(0)
-        for k in range(12):
+        for k in range(4):
             busy = (ws[k, 1] - ws[k, 0]).mean() / ghz / 1e3
             lag0 = (ws[k, 0] - first_start).mean() / ghz / 1e3
             lag1 = (ws[k, 1] - first_done).mean() / ghz / 1e3
-            quad = (st * 12 + k + 2) & 3       # warp index & 3 = SM sub-partition
-            print(f"   set {st} grp {k // 4} quad {quad} | {busy:5.2f} | "
-                  f"{lag0:5.2f} | {lag1:5.2f}")
+            quad = (st * 4 + k + 2) & 3        # warp index & 3 = SM sub-partition
+            print(f"   set {st} quad {quad} | {busy:5.2f} | {lag0:5.2f} | "
+                  f"{lag1:5.2f}")
 
 
 if __name__ == "__main__":
