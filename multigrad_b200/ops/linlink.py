@@ -196,17 +196,18 @@ class LinLinkPlan:
     def evaluate(self, params: torch.Tensor, mode: int, reduce: bool = True):
         p = params.detach().to(self.device, torch.float32).contiguous()
         assert p.numel() == self.NP
-        out = {"sumstats": torch.empty(self.K, device=self.device)}
+        f32 = dict(dtype=torch.float32, device=self.device)
+        out = {"sumstats": torch.empty(self.K, **f32)}
         a = MgbLinArgs()
         a.mode = mode
         a.reduce = 1 if (reduce and self.world > 1) else 0
         a.params = p.data_ptr()
         a.out_sumstats = out["sumstats"].data_ptr()
-        out["jac"] = torch.zeros(self.K, self.NP, device=self.device)
+        out["jac"] = torch.zeros(self.K, self.NP, **f32)
         a.out_jac = out["jac"].data_ptr()
         if mode >= _lib.MODE_LOSS_GRAD:
-            out["loss"] = torch.empty(1, device=self.device)
-            out["grad"] = torch.empty(self.NP, device=self.device)
+            out["loss"] = torch.empty(1, **f32)
+            out["grad"] = torch.empty(self.NP, **f32)
             a.out_loss, a.out_grad = (out["loss"].data_ptr(),
                                       out["grad"].data_ptr())
         self.launch(a)

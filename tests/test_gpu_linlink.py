@@ -258,6 +258,26 @@ def test_joins_a_device_resident_group():
                           atol=0.02), traj[-1]
 
 
+def test_float64_default_dtype_does_not_change_the_buffers():
+    """Buffers handed to the C ABI are float32 whatever torch's default is."""
+    from multigrad_b200.models import SMFModel, smf
+    gpu, _, p = make(20_000, 5)
+    s0, j0 = gpu.calc_sumstats_and_jac_from_params(p)
+    data = smf.make_smf_data(10_000, comm=SELF, device=dev())
+    ref = SMFModel(aux_data=data, comm=SELF, device=dev())
+    l0, g0 = ref.calc_loss_and_grad_from_params([-1.9, 0.3])
+    old = torch.get_default_dtype()
+    torch.set_default_dtype(torch.float64)
+    try:
+        s1, j1 = gpu.calc_sumstats_and_jac_from_params(p)
+        l1, g1 = ref.calc_loss_and_grad_from_params([-1.9, 0.3])
+    finally:
+        torch.set_default_dtype(old)
+    assert s1.dtype == torch.float32 and torch.equal(s0, s1)
+    assert torch.equal(j0, j1)
+    assert torch.equal(l0, l1) and torch.equal(g0, g1)
+
+
 def test_fp8_gate_decision_is_reproducible():
     """The FP8 gate (tools/fp8_gate.py): MXFP8 features are emulated exactly
     on the bf16 kernel; the committed decision (profiles/linlink_fp8_gate.json)
