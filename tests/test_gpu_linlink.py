@@ -264,7 +264,7 @@ def test_float64_default_dtype_does_not_change_the_buffers():
     gpu, _, p = make(20_000, 5)
     s0, j0 = gpu.calc_sumstats_and_jac_from_params(p)
     data = smf.make_smf_data(10_000, comm=SELF, device=dev())
-    ref = SMFModel(aux_data=data, comm=SELF, device=dev())
+    ref = SMFModel(aux_data=data, comm=SELF, device=dev(), deterministic=True)
     l0, g0 = ref.calc_loss_and_grad_from_params([-1.9, 0.3])
     old = torch.get_default_dtype()
     torch.set_default_dtype(torch.float64)
