@@ -1401,6 +1401,7 @@ extern "C" int mgb_erfbin_step(const MgbErfBinModel* model,
       return e && e[0] == '1';
     }();
     if (deterministic) a.flags |= MGB_STEP_STATIC_SPLIT;
+    a.flags |= md.step_flags;
   }
   MGB_REQUIRE(md.nbins >= 1 && md.nbins <= MGB_MAX_BINS, MGB_ETOOBIG,
               "mgb_erfbin_step: nbins=%d outside [1,%d]", md.nbins,

@@ -138,6 +138,11 @@ typedef struct MgbErfBinModel {
   float x0;              /* centring constant: the kernel works on x - x0;
                             pick a value near the bulk of the data (any value
                             is valid, 0 disables centring)                  */
+  int32_t step_flags;    /* MGB_STEP_* bits ORed into EVERY launch for this
+                            model, whichever entry point builds its arguments
+                            (e.g. MGB_STEP_STATIC_SPLIT for bit-reproducible
+                            host evaluations and L-BFGS-B sessions)         */
+  int32_t reserved0;
   double edges[MGB_MAX_BINS + 1]; /* fp64: the scaled edge constants are
                             formed in double, and exactly uniform spacing (as
                             from linspace) enables the Gaussian recurrence    */

@@ -59,6 +59,7 @@ class MgbErfBinModel(C.Structure):
         ("mu_idx", C.c_int32), ("sig_idx", C.c_int32),
         ("sigma_link", C.c_int32), ("loss_kind", C.c_int32),
         ("loss_eps", C.c_float), ("x0", C.c_float),
+        ("step_flags", C.c_int32), ("reserved0", C.c_int32),
         ("edges", C.c_double * (MGB_MAX_BINS + 1)),
         ("norm", C.c_float * MGB_MAX_BINS),
         ("target", C.c_float * MGB_MAX_BINS),

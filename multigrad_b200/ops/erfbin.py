@@ -103,10 +103,22 @@ class ErfBinPlan:
         self.world = peer_table.world if peer_table is not None else 1
         self._scratch = {}
         self._scratch_for(1)
-        # True: fully static tile split, bit-reproducible results (2-3%
-        # slower); also forced by MULTIGRAD_B200_DETERMINISTIC=1 (read by the
-        # library).  See MGB_STEP_STATIC_SPLIT in include/multigrad_b200.h.
-        self.deterministic = False
+
+    # True: fully static tile split, bit-reproducible results (2-3% slower);
+    # also forced by MULTIGRAD_B200_DETERMINISTIC=1 (read by the library).
+    # Kept in the model struct (MgbErfBinModel.step_flags) so that it reaches
+    # every native entry point, the host evaluations and L-BFGS-B sessions
+    # included, not only launches whose arguments are built here.
+    @property
+    def deterministic(self) -> bool:
+        return bool(self.model.step_flags & _lib.STEP_STATIC_SPLIT)
+
+    @deterministic.setter
+    def deterministic(self, value: bool) -> None:
+        if value:
+            self.model.step_flags |= _lib.STEP_STATIC_SPLIT
+        else:
+            self.model.step_flags &= ~_lib.STEP_STATIC_SPLIT
 
     # ------------------------------------------------------------------ utils
     def set_target(self, target, inv_err=None) -> None:
@@ -133,10 +145,6 @@ class ErfBinPlan:
     def launch(self, args: MgbStepArgs) -> None:
         global _LAUNCHES
         s = self._scratch_for(args.batch)
-        if self.deterministic:
-            args.flags |= _lib.STEP_STATIC_SPLIT
-        else:
-            args.flags &= ~_lib.STEP_STATIC_SPLIT
         if torch.cuda.current_device() != self.device.index:
             torch.cuda.set_device(self.device)     # one process per GPU
         rc = self.lib.mgb_erfbin_step(
