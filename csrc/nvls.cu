@@ -260,6 +260,9 @@ namespace {
 #define NV_UNROLL 8
 #endif
 #define NV_RESIDENT_CTAS 16
+#ifndef NV_PIPE_DEFAULT
+#define NV_PIPE_DEFAULT 0
+#endif
 
 __device__ __forceinline__ float4 mc_ld_reduce_f4(const float4* p) {
   float4 v;
@@ -423,6 +426,189 @@ nvls_allreduce_f32_kernel(const MgbPeerTable pt, float4* __restrict__ uc,
   }
 }
 
+
+// ---- staged all-reduce as a pipeline (large ordinary tensors) --------------
+// The copy phases want every SM, the in-switch phase a few CTAs with many
+// requests in flight (see NV_RESIDENT_CTAS), and in the kernel above neither
+// overlaps the other.  Here the roles are split inside ONE co-resident grid:
+//   copier CTAs  each stage one part of one 2 MiB chunk into the bound buffer,
+//                count themselves in on staged[c], and copy the same part
+//                back out as soon as reduced[c] carries the epoch
+//   reducer CTAs own chunks c = r, r + R, ...: wait for the local copiers of
+//                the chunk, exchange "staged" flags with the peers, reduce the
+//                rank's sub-slice through the switch, exchange "reduced"
+//                flags, release the chunk to the copiers
+// so chunk c-R is copied out while chunk c crosses the switch.  OPT-IN
+// (MULTIGRAD_B200_NVLS_PIPELINE=1): measured on 2 GPUs only, 148 -> 123 us at
+// 32 MiB and 253 -> 234 us at 64 MiB against the kernel above.  The grid is launched cooperatively: every CTA has to be resident
+// because reducers wait for ALL copiers of a chunk.
+#define NV_PIPE_CHUNK4 131072          // float4 per chunk (2 MiB)
+#define NV_PIPE_MAX_CHUNKS 64
+#define NV_PIPE_REDUCERS 16
+#define NV_CTRL_STAGED 64              // uint32 words of the control block
+#define NV_CTRL_REDUCED 128
+
+__device__ __forceinline__ unsigned ld_acquire_gpu_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v)
+               : "memory");
+}
+// thread 0 of a CTA waits until *p == want (bounded like every peer wait)
+__device__ __forceinline__ void cta_wait_word(const MgbPeerTable& pt,
+                                              const unsigned* p,
+                                              unsigned want) {
+  if (threadIdx.x == 0 && ld_acquire_gpu_u32(p) != want) {
+    const unsigned long long t0 = mgb_globaltimer_ns();
+    const unsigned long long limit =
+        (unsigned long long)pt.spin_timeout_ms * 1000000ull;
+    unsigned it = 0;
+    while (ld_acquire_gpu_u32(p) != want) {
+      if ((++it & 63u) == 0u) {
+        if (mgb_globaltimer_ns() - t0 > limit) {
+          mgb_st_sys_u32(mgb_ctrl(pt, pt.rank) + MGB_CTRL_ERROR, 1u);
+          break;
+        }
+        __nanosleep(100);
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(NV_BLOCK, 2)
+nvls_pipelined_f32_kernel(const MgbPeerTable pt, float4* __restrict__ uc,
+                          float4* __restrict__ mc, float* __restrict__ data,
+                          long long n4, long long tail_start, int ntail,
+                          int nred) {
+  __shared__ unsigned s_epoch;
+  const int tid = threadIdx.x;
+  const int W = pt.world, me = pt.rank;
+  unsigned* ctrl = mgb_ctrl(pt, me);
+  if (tid == 0) s_epoch = mgb_ld_sys_u32(ctrl + MGB_CTRL_EPOCH) + 1u;
+  __syncthreads();
+  const unsigned epoch = s_epoch;
+  unsigned* staged = ctrl + NV_CTRL_STAGED;
+  unsigned* reduced = ctrl + NV_CTRL_REDUCED;
+  const long long n4t = n4 + (ntail ? 1 : 0);
+  const int nchunks = (int)((n4t + NV_PIPE_CHUNK4 - 1) / NV_PIPE_CHUNK4);
+  const int ncop = (int)gridDim.x - nred;
+  float4* d4 = reinterpret_cast<float4*>(data);
+  if ((int)blockIdx.x < nred) {
+    // ------------------------------------------------------------- reducer
+    for (int c = blockIdx.x; c < nchunks; c += nred) {
+      cta_wait_word(pt, staged + c, (unsigned)(ncop / nchunks));
+      if (tid == 0) staged[c] = 0u;          // nobody adds again in this call
+      cta_rank_barrier(pt, epoch, (unsigned)c);
+      const long long lo = (long long)c * NV_PIPE_CHUNK4;
+      const long long hi = min(lo + (long long)NV_PIPE_CHUNK4, n4t);
+      const long long sub = (hi - lo + W - 1) / W;
+      const long long slo = lo + sub * me;
+      const long long shi = min(slo + sub, hi);
+      for (long long i = slo + tid; i < shi;
+           i += (long long)NV_UNROLL * NV_BLOCK) {
+        float4 v[NV_UNROLL];
+#pragma unroll
+        for (int k = 0; k < NV_UNROLL; ++k)
+          if (i + k * NV_BLOCK < shi)
+            v[k] = mc_ld_reduce_f4(mc + i + k * NV_BLOCK);
+#pragma unroll
+        for (int k = 0; k < NV_UNROLL; ++k)
+          if (i + k * NV_BLOCK < shi) mc_st_f4(mc + i + k * NV_BLOCK, v[k]);
+      }
+      cta_rank_barrier(pt, epoch, (unsigned)(NV_MAX_CTAS + c));
+      if (tid == 0) st_release_gpu_u32(reduced + c, epoch);
+    }
+  } else {
+    // -------------------------------------------------------------- copier
+    // copier k owns part k / nchunks of chunk k % nchunks: all chunks are
+    // staged side by side (a schedule in rounds of nred chunks, staging the
+    // first round first, measured slower: 249 vs 234 us at 64 MiB on 2 GPUs)
+    const int k = (int)blockIdx.x - nred;
+    const int parts = ncop / nchunks;
+    if (k < parts * nchunks) {
+      const int c = k % nchunks, part = k / nchunks;
+      const long long lo = (long long)c * NV_PIPE_CHUNK4;
+      const long long hi = min(lo + (long long)NV_PIPE_CHUNK4, n4t);
+      const long long k0 = (long long)part * NV_BLOCK + tid;
+      const long long stride = (long long)parts * NV_BLOCK;
+      for (long long i = lo + k0; i < hi; i += 4 * stride) {
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const long long j = i + q * stride;
+          if (j < hi) {
+            if (j < n4) {
+              v[q] = d4[j];
+            } else {
+              v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (ntail > 0) v[q].x = data[tail_start];
+              if (ntail > 1) v[q].y = data[tail_start + 1];
+              if (ntail > 2) v[q].z = data[tail_start + 2];
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (i + q * stride < hi) uc[i + q * stride] = v[q];
+      }
+      __syncthreads();
+      if (tid == 0) {
+        __threadfence_system();
+        atomicAdd(staged + c, 1u);
+      }
+      cta_wait_word(pt, reduced + c, epoch);
+      for (long long i = lo + k0; i < hi; i += 4 * stride) {
+        float4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (i + q * stride < hi) v[q] = __ldcv(uc + i + q * stride);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const long long j = i + q * stride;
+          if (j < hi) {
+            if (j < n4) {
+              d4[j] = v[q];
+            } else {
+              if (ntail > 0) data[tail_start] = v[q].x;
+              if (ntail > 1) data[tail_start + 1] = v[q].y;
+              if (ntail > 2) data[tail_start + 2] = v[q].z;
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned t = atomicAdd(ctrl + MGB_CTRL_TICKET, 1u);
+    if (t == gridDim.x - 1) {
+      ctrl[MGB_CTRL_TICKET] = 0u;
+      __threadfence();
+      mgb_st_sys_u32(ctrl + MGB_CTRL_EPOCH, epoch);
+    }
+  }
+}
+
+// co-resident grid of the pipelined kernel on the current device (0: none)
+int nvls_pipe_grid() {
+  int dev = 0, sms = 0, per_sm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) !=
+      cudaSuccess)
+    return 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+          &per_sm, nvls_pipelined_f32_kernel, NV_BLOCK, 0) != cudaSuccess)
+    return 0;
+  long long g = (long long)sms * per_sm;
+  if (g > NV_MAX_CTAS) g = NV_MAX_CTAS;
+  return (int)g;
+}
+
 }  // namespace
 
 extern "C" int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc,
@@ -461,6 +647,31 @@ extern "C" int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc,
     if (c >= 1 && c <= NV_MAX_CTAS && c < ctas) ctas = c;
   }
   if (ctas < 1) ctas = 1;
+  // large ordinary tensors: copy phases and switch phase pipelined per chunk
+  {
+    static const int pipe_mode = [] {
+      const char* e = getenv("MULTIGRAD_B200_NVLS_PIPELINE");
+      return e ? atoi(e) : NV_PIPE_DEFAULT;
+    }();
+    const long long nchunks = (n4t + NV_PIPE_CHUNK4 - 1) / NV_PIPE_CHUNK4;
+    if (!inplace && pipe_mode && nchunks >= NV_PIPE_REDUCERS &&
+        nchunks <= NV_PIPE_MAX_CHUNKS) {
+      const int grid = nvls_pipe_grid();
+      if (grid >= 4 * NV_PIPE_REDUCERS &&
+          grid - NV_PIPE_REDUCERS >= (int)nchunks) {   // >= 1 copier per chunk
+        MgbPeerTable ptv = *pt;
+        float4* ucp = (float4*)uc;
+        float4* mcp = (float4*)mc;
+        int nred = NV_PIPE_REDUCERS;
+        void* args[] = {&ptv, &ucp, &mcp, &data, &n4, &tail_start, &ntail,
+                        &nred};
+        MGB_CUDA_CHECK(cudaLaunchCooperativeKernel(
+            (void*)nvls_pipelined_f32_kernel, dim3(grid), dim3(NV_BLOCK), args,
+            0, (cudaStream_t)stream));
+        return MGB_OK;
+      }
+    }
+  }
   if (inplace) {
     float4* mcd = (float4*)((char*)mc + (d0 - u0));
     nvls_allreduce_f32_kernel<true><<<(unsigned)ctas, NV_BLOCK, 0,

@@ -76,6 +76,20 @@ def main():
         x = torch.randn(n, device=dev)
         xs = mc_x[:n]
         xs.copy_(x)
+        # correctness of the staged and resident paths on a pattern whose sum
+        # is known in closed form (ragged length on purpose)
+        nn = n - 3
+        idx = torch.arange(nn, device=dev, dtype=torch.float32)
+        pat = (idx % 1013.0) * 0.25 + float(comm.rank + 1)
+        want = (idx % 1013.0) * 0.25 * world + world * (world + 1) / 2.0
+        y = pat.clone()
+        ar.all_reduce_sum_(y, comm, algo=4)
+        ys = mc_x[:nn]
+        ys.copy_(pat)
+        ar.all_reduce_sum_(ys, comm, algo=4)
+        torch.cuda.synchronize()
+        ok = bool(torch.equal(y, want)) and bool(torch.equal(ys, want))
+        assert all(comm.allgather(ok)), f"wrong sums at {mb} MiB"
         nccl = timed(lambda: dist.all_reduce(x, group=comm.group))
         row = {"mb": mb, "n_gpus": world, "nccl_us": round(nccl, 1)}
         for c in ctas:
