@@ -5,15 +5,19 @@
 // so that  d s_k / d theta_j = c_k * sum_h (g_{k+1,h} - g_{k,h}) W[h,j]
 // is a tall-skinny GEMM with the *object axis as the MMA K dimension*:
 //
-//   MMA #1 (forward)   D1[128 objects, 16]  = Wtile[128 x P]  . Theta[P x 16]
-//   MMA #2 (Jacobian)  D2[32 rows, P]      += G[32 x 128 obj] . Wtile[128 x P]
+//   forward   mu[128 objects]      = Wtile[128 x P] . theta        (3 columns)
+//   Jacobian  D2[P, 32 rows]      += Wtile^T[P x 128 obj] . G^T[128 obj x 32]
 //
-// The same TMA-loaded, 128B-swizzled W tile is operand A (K-major) of #1 and
-// operand B (MN-major) of #2; theta is split into three bf16 planes and g
-// into two, so both products carry ~fp32 / ~2^-17 accuracy with bf16 inputs.
-// Accumulators live in TMEM; CUDA cores only evaluate erfc / exp per
-// (object, edge) and convert g to bf16.  W streams through HBM exactly once
-// per step (the reference's forward + VJP would stream it twice).
+// The Jacobian product runs on tcgen05 (UMMA, accumulators in TMEM): the
+// TMA-loaded, 128B-swizzled W tile is its MN-major A operand, the Gaussian
+// weights G (two bf16 planes per edge, ~2^-17 accuracy) its K-major B operand.
+// The forward product has only three useful columns (theta as three bf16
+// planes, fp32-grade); as a UMMA it re-read the whole tile through the tensor
+// cores' operand path, which then bounded the kernel, so the compute warps do
+// it themselves with ldmatrix + mma.sync on the same shared-memory tile.
+// CUDA cores evaluate erfc / exp per (object, edge) and convert g to bf16.
+// W streams through HBM exactly once per step (the reference's forward + VJP
+// would stream it twice).
 //
 // Reference counterpart: jax.vjp of a user sumstats function with a
 // per-object linear predictor (OnePointModel._vjp, multigrad.py:508-538).
@@ -257,14 +261,15 @@ linlink_selftest_kernel(const __grid_constant__ CUtensorMap wmap,
 
 // ===========================================================================
 // The fused step.
-//   warp 0        TMA producer (W tiles, 128 objects x P features, SW128)
-//   warp 1        UMMA issuer (both products) + TMEM owner
-//   warps 2..13   compute: 3 edge groups x 4 TMEM lane quadrants; thread =
-//                 one object of the tile and the <= 4 edges of its group
-// Pipeline per tile (stage s of LL_STAGES):
-//   TMA -> full_w[s] -> UMMA#1 -> mu_full[s] -> compute (tcgen05.ld mu, erfc,
-//   g -> bf16 hi/lo into G[s]) -> g_full[s] -> UMMA#2 (accumulates D2) ->
-//   empty[s] -> TMA ...
+//   warp 0        producer: TMA of the W tile (128 objects x P features,
+//                 SW128) + bulk copies of the tile's x / weights
+//   warp 1        UMMA issuer (Jacobian product) + TMEM owner
+//   warps 2..     compute: `sets` x 4 warps; a warp = 32 objects of a tile and
+//                 all of its <= 12 edges
+// Pipeline per tile (W stage s of LL_STAGES, G buffer gb of the G ring):
+//   TMA -> full_w[s] -> compute (ldmatrix + mma.sync for mu, erfc, g -> bf16
+//   hi/lo into G[gb]) -> g_full[gb] -> Jacobian UMMAs (accumulate D2) ->
+//   empty[s], g_free[gb] -> TMA ...
 // ===========================================================================
 // pipeline depth: the W tile of a stage lives from its TMA until the Jacobian
 // product has consumed it, so the depth has to cover the HBM latency

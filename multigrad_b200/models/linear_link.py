@@ -7,9 +7,10 @@ functions of object properties (a constant column reproduces the plain shift
 of :class:`SMFModel`; more columns give a mass- or environment-dependent
 stellar-to-halo-mass relation).  ``d sumstats / d theta`` is a tall-skinny
 GEMM over the object axis, which the CUDA path runs on the tensor cores
-(``csrc/linlink.cu``: TMA-streamed bf16 feature tiles, tcgen05 UMMA with TMEM
-accumulators), fused with the erfc evaluation, the cross-GPU reduction and
-the optimiser.  Features are stored in bf16; that quantised matrix *is* the
+(``csrc/linlink.cu``: TMA-streamed bf16 feature tiles, the forward product on
+ldmatrix + mma.sync inside the compute warps, the Jacobian product on tcgen05
+UMMA with TMEM accumulators), fused with the erfc evaluation, the cross-GPU
+reduction and the optimiser.  Features are stored in bf16; that quantised matrix *is* the
 model (forward and Jacobian use the same values), and theta is split into
 three bf16 planes so the forward product is accurate to fp32.
 
