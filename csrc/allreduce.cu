@@ -82,7 +82,22 @@ ll_bcast_kernel(const MgbPeerTable pt, float* __restrict__ data, int n,
   if (tid == 0) s_epoch = mgb_ld_sys_u32(ctrl + MGB_CTRL_EPOCH) + 1u;
   __syncthreads();
   const unsigned epoch = s_epoch, parity = epoch & 1u;
+  // Ready-first: every receiver announces itself with one tagged word in a
+  // unit of its own (the last one; data never uses it), and the root pushes
+  // only when all have.  A broadcast is one-way, so a root that pushed at once
+  // could overwrite words a slow peer has not read yet: its own all-reduce
+  // contribution of two collectives ago, or -- if it only acknowledged
+  // afterwards -- a pending acknowledgement.  With the announcement nobody
+  // finishes collective e+1 before everybody has finished e, which is the
+  // invariant the two parities rest on (tools/ll_protocol_model.py explores
+  // the schedules: this form is clean, push-then-acknowledge is not).
+  const unsigned ready_unit = pt.ll_units - 1u;
   if (pt.rank == root) {
+    for (int s = tid; s < W; s += nt)
+      if (s != root)
+        (void)mgb_ll_wait(pt, mgb_ll_slot(pt, root, parity, s, ready_unit),
+                          epoch);
+    __syncthreads();
     for (int i = tid; i < n * (W - 1); i += nt) {
       const int pi = i / n, u = i - pi * n;
       int dst = root + 1 + pi;
@@ -91,22 +106,13 @@ ll_bcast_kernel(const MgbPeerTable pt, float* __restrict__ data, int n,
                      ((unsigned long long)epoch << 32) |
                          __float_as_uint(data[u]));
     }
-    // back-pressure: a broadcast is one-way, so without this the root could
-    // run two broadcasts ahead and overwrite a parity slot that a slow
-    // receiver has not read yet.  Every receiver acknowledges (one tagged
-    // word into the root's slot [parity][receiver][0]); the root leaves only
-    // when all have.
-    for (int s = tid; s < W; s += nt)
-      if (s != root)
-        (void)mgb_ll_wait(pt, mgb_ll_slot(pt, root, parity, s, 0u), epoch);
   } else {
+    if (tid == 0)
+      mgb_st_sys_u64(mgb_ll_slot(pt, root, parity, pt.rank, ready_unit),
+                     (unsigned long long)epoch << 32);
     for (int j = tid; j < n; j += nt)
       data[j] = __uint_as_float(mgb_ll_wait(
           pt, mgb_ll_slot(pt, pt.rank, parity, root, (unsigned)j), epoch));
-    __syncthreads();
-    if (tid == 0)
-      mgb_st_sys_u64(mgb_ll_slot(pt, root, parity, pt.rank, 0u),
-                     (unsigned long long)epoch << 32);
   }
   __syncthreads();
   if (tid == 0) mgb_st_sys_u32(ctrl + MGB_CTRL_EPOCH, epoch);
@@ -453,9 +459,10 @@ extern "C" int mgb_bcast_f32(const MgbPeerTable* pt, float* data, uint32_t n,
   MGB_REQUIRE(root >= 0 && root < pt->world, MGB_EINVAL,
               "mgb_bcast_f32: bad root %d", root);
   if (pt->world == 1 || n == 0) return MGB_OK;
-  MGB_REQUIRE(n <= pt->ll_units, MGB_ETOOBIG,
+  // (the last unit carries the receivers' announcements)
+  MGB_REQUIRE(n + 1u <= pt->ll_units, MGB_ETOOBIG,
               "mgb_bcast_f32: %u floats exceed the LL capacity %u", n,
-              pt->ll_units);
+              pt->ll_units - 1u);
   ll_bcast_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(*pt, data, (int)n,
                                                        root);
   MGB_CUDA_CHECK(cudaGetLastError());

@@ -106,9 +106,10 @@ int mgb_allreduce_sum_nvls(const MgbPeerTable* pt, void* uc, void* mc,
 
 /* push `n` floats from `root` to every rank over NVLink (replaces a pickled
  * parameter bcast like multigrad/bfgs.py:72-77 or mpi4jax.bcast,
- * multigrad/mpi4jax/multigrad.py:52).  Non-root ranks wait on the GPU until
- * the data arrives and acknowledge; the root returns once every rank has, so
- * back-to-back broadcasts cannot overrun a slow receiver. */
+ * multigrad/mpi4jax/multigrad.py:52).  Ready-first: every non-root rank
+ * announces itself (one tagged word) and waits on the GPU for the data; the
+ * root pushes once all have announced, so no collective can overrun a slow
+ * rank whatever the mix of collectives and roots.  n <= ll_units - 1. */
 int mgb_bcast_f32(const MgbPeerTable* pt, float* data, uint32_t n, int root,
                   void* stream);
 
